@@ -1,0 +1,166 @@
+/*
+ * vxrt.h — C ABI of the B200-native voxel ray-tracing hot path.
+ *
+ * This is the drop-in boundary for the reference's `src/render` module
+ * (someguynamedjosh/raytrace).  Each entry point names the reference interface
+ * it replaces (file:line under /root/reference).  Plain pointers and sizes
+ * only; the caller owns every host pointer, the library owns all device memory.
+ * Every call returns VXRT_OK (0) or a negative VxrtStatus; vxrt_last_error()
+ * gives the text.  A handle is bound to one GPU and one CUDA stream and is not
+ * thread-safe (the reference is single-threaded: Rc<Core>, render/mod.rs:1,39).
+ *
+ * There is NO CPU fallback: without a CUDA device vxrt_create fails with
+ * VXRT_ERR_CUDA.
+ */
+#ifndef VXRT_H
+#define VXRT_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VXRT_ABI_VERSION 1
+
+typedef enum VxrtStatus {
+    VXRT_OK = 0,
+    VXRT_ERR_INVALID = -1,   /* bad argument / configuration             */
+    VXRT_ERR_CUDA = -2,      /* CUDA runtime error (text in last_error)   */
+    VXRT_ERR_STATE = -3,     /* call made in the wrong order              */
+    VXRT_ERR_SIZE = -4       /* host buffer too small                     */
+} VxrtStatus;
+
+/* Truncations of raytrace.comp:main (:320-350).  Only FULL is reference behaviour. */
+typedef enum VxrtMode { VXRT_MODE_PRIMARY = 0, VXRT_MODE_SHADOW = 1, VXRT_MODE_FULL = 2 } VxrtMode;
+
+/* vxrt_create flags */
+#define VXRT_FLAG_HIT_BUFFERS   0x1u  /* keep per-pixel hit voxel/face/word/t/steps/rays (parity + stats) */
+#define VXRT_FLAG_DENOISE       0x2u  /* run the 6 bilateral passes (pipeline.rs:98-115)                    */
+#define VXRT_FLAG_FINALIZE      0x4u  /* run finalize.comp -> RGBA8 output (pipeline.rs:117-123)            */
+#define VXRT_FLAG_ACCUMULATE    0x8u  /* temporal accumulation of `light` (extension)          */
+#define VXRT_FLAG_PONG_SWAP     0x10u /* reproduce descriptor_sets.rs:37-39 (odd passes read swapped images)*/
+#define VXRT_FLAG_REF_ROWS      0x20u /* leave the rows the reference grid (W/8,H/8+1) never writes untouched*/
+
+/* Replaces the compile-time constants of src/render/constants.rs:9-10,22-31 and the
+ * shader constants raytrace.comp:37-60, which become run-time parameters. */
+typedef struct VxrtConfig {
+    uint32_t abi_version;        /* VXRT_ABI_VERSION                                        */
+    int32_t  width, height;      /* frame size (constants.rs:9-10: 1024x1024)               */
+    int32_t  nx, ny, nz;         /* voxel window, powers of two >= 64 (ROOT_BLOCK_SIZE 256) */
+    int32_t  mode;               /* VxrtMode                                                */
+    uint32_t flags;              /* VXRT_FLAG_*                                             */
+    int32_t  max_steps;          /* raytrace.comp:109, 0 -> 2048                            */
+    int32_t  device;             /* CUDA device ordinal                                     */
+    int32_t  row_begin, row_end; /* G-buffer rows this handle renders (image-space shard);
+                                    0,0 -> whole frame.  Output rows are height-1-row.      */
+    int32_t  reserved[4];
+} VxrtConfig;
+
+/* Byte-compatible with `RaytraceUniformData` (#[repr(C)], 192 B,
+ * src/render/pipeline/structs.rs:3-31) so the Rust side can pass &uniform_data. */
+typedef struct VxrtFrameParams {
+    float    sun_angle;              /*   0 */
+    uint32_t seed;                   /*   4 */
+    uint64_t _padding0;              /*   8 */
+    float    origin[3];  uint32_t _padding1;   /*  16 */
+    float    forward[3]; uint32_t _padding2;   /*  32 */
+    float    up[3];      uint32_t _padding3;   /*  48  (pre-scaled by 0.4, pipeline.rs:198) */
+    float    right[3];   uint32_t _padding4;   /*  64  (pre-scaled by 0.4, pipeline.rs:199) */
+    float    old_origin[3];       uint32_t _padding5;  /*  80  unread by the shaders */
+    float    old_transform_c0[3]; uint32_t _padding6;  /*  96  unread */
+    float    old_transform_c1[3]; uint32_t _padding7;  /* 112  unread */
+    float    old_transform_c2[3]; uint32_t _padding8;  /* 128  unread */
+    int32_t  region_offset[3];    uint32_t _padding9;  /* 144  unread */
+    int32_t  rotation[3];         uint32_t _padding10; /* 160  shader name: lr (window centre) */
+    int32_t  space_offset[3];     uint32_t _padding11; /* 176  unread */
+} VxrtFrameParams;
+
+/* One voxel edit in WORLD coordinates (window texel = (world + N/2) mod N). */
+typedef struct VxrtEdit { int32_t x, y, z; uint32_t word; } VxrtEdit;
+
+typedef enum VxrtBufferId {
+    VXRT_BUF_OUTPUT = 0,     /* RGBA8   w*h*4   final image, y flipped (finalize.comp:60-63)   */
+    VXRT_BUF_LIGHTING = 1,   /* RGBA16  w*h*8   lighting_buffer after the last pass run        */
+    VXRT_BUF_DEPTH = 2,      /* R16UI   w*h*2                                                  */
+    VXRT_BUF_NORMAL = 3,     /* R8UI    w*h                                                    */
+    VXRT_BUF_ALBEDO = 4,     /* RGBA8   w*h*4                                                  */
+    VXRT_BUF_EMISSION = 5,   /* RGBA8   w*h*4                                                  */
+    VXRT_BUF_FOG = 6,        /* RGBA8   w*h*4                                                  */
+    VXRT_BUF_HIT_VOXEL = 7,  /* int32x3 w*h*12  floor(position) at loop exit (HIT_BUFFERS)     */
+    VXRT_BUF_HIT_FACE = 8,   /* u8      w*h     0..5, 16 = air                                 */
+    VXRT_BUF_HIT_WORD = 9,   /* u32     w*h*4   packed material word, 0 on air                 */
+    VXRT_BUF_HIT_T = 10,     /* f32     w*h*4   primary hit distance                           */
+    VXRT_BUF_STEPS = 11,     /* u32     w*h*4   march iterations over all rays of the pixel    */
+    VXRT_BUF_RAYS = 12,      /* u8      w*h     trace_ray calls of the pixel                   */
+    VXRT_BUF_ACCUM = 13,     /* f32x4   w*h*16  running sum of light + frame count             */
+    VXRT_BUF_LIGHTING_RAW = 14, /* RGBA16 w*h*8 lighting as written by the trace pass          */
+    VXRT_BUF_COUNT_
+} VxrtBufferId;
+
+/* Counters of the last rendered frame (whole rows this handle rendered). */
+typedef struct VxrtFrameStats {
+    uint64_t rays, steps, hits, noise_fetches;
+    uint64_t limit_exhausted;    /* rays that ran out of max_steps (reference UB) */
+    float    trace_ms, denoise_ms, finalize_ms, total_ms;   /* CUDA-event times of the last frame */
+} VxrtFrameStats;
+
+typedef struct VxrtHandle VxrtHandle;
+
+/* ---- construction / teardown -------------------------------------------------------- */
+/* replaces render::create_instance (src/render/mod.rs:36-43) + Pipeline::new (pipeline.rs:36-76)
+ * + RenderData::create (render_data.rs:165-201), minus window/swapchain. */
+int  vxrt_create(const VxrtConfig* cfg, VxrtHandle** out);
+/* replaces Drop for Pipeline/Core (pipeline.rs:258-277, core.rs:88-112) */
+void vxrt_destroy(VxrtHandle* h);
+const char* vxrt_last_error(const VxrtHandle* h);   /* h may be NULL: error of the last failed create */
+int  vxrt_abi_version(void);
+
+/* ---- world upload ------------------------------------------------------------------- */
+/* One 64^3 chunk at window chunk coords (cx,cy,cz) in [0, n/64): replaces the per-chunk
+ * copy_materials/copy_minefield of make_world_upload_buffers (render_data.rs:221-241).
+ * materials: 64^3 u32, x fastest (PackedChunkData, chunk.rs:52-56).
+ * minefield: 64^3 u8 or NULL -> built on the GPU with the pack_into rule (chunk.rs:125-184). */
+int  vxrt_upload_chunk(VxrtHandle* h, int cx, int cy, int cz, const uint32_t* materials, const uint8_t* minefield);
+/* Whole window at once ([nz][ny][nx], x fastest); minefield NULL -> built on the GPU. */
+int  vxrt_upload_world(VxrtHandle* h, const uint32_t* materials, const uint8_t* minefield);
+/* A 16-thick slab along `axis` at window texel offset `offset` (multiple of 16): replaces
+ * TerrainUploadManager::upload_slice's copy_buffer_to_image_offset (terrain_upload.rs:212-267).
+ * Slab layout: x fastest, extents = window dims with `axis` replaced by 16. */
+int  vxrt_upload_slice(VxrtHandle* h, int axis, int offset, const uint32_t* materials, const uint8_t* minefield);
+/* Seeded synthetic worlds generated on the device (kind 0 = heightmap, 1 = biome). */
+int  vxrt_generate_world(VxrtHandle* h, int kind, uint32_t seed);
+/* Rebuild every chunk's minefield from the material words (pack_into, chunk.rs:125-184). */
+int  vxrt_rebuild_minefield(VxrtHandle* h);
+int  vxrt_read_world(VxrtHandle* h, uint32_t* materials, uint8_t* minefield);   /* either may be NULL */
+/* replaces create_blue_noise (render_data.rs:110-133): 512*512 RGBA8 */
+int  vxrt_upload_blue_noise(VxrtHandle* h, const uint8_t* rgba, size_t nbytes);
+
+/* ---- edits (no reference equivalent beyond set_block + pack_into, chunk.rs:115-184) -- */
+/* Writes the words, then rebuilds the minefield of every touched 64^3 chunk. */
+int  vxrt_apply_edits(VxrtHandle* h, const VxrtEdit* edits, size_t n);
+/* Same with the edit list already on the device (e.g. after an NCCL broadcast). */
+int  vxrt_apply_edits_device(VxrtHandle* h, const void* d_edits, size_t n);
+
+/* ---- per frame ---------------------------------------------------------------------- */
+/* replaces the uniform fill + mapped-buffer memcpy of draw_frame (pipeline.rs:195-211) */
+int  vxrt_set_frame(VxrtHandle* h, const VxrtFrameParams* p);
+/* replaces the submit of the pre-recorded command buffer (pipeline.rs:78-132,229-235):
+ * trace -> [6x denoise] -> [finalize], asynchronous on the handle's stream. */
+int  vxrt_render_frame(VxrtHandle* h);
+/* replaces wait_for_fences (pipeline.rs:162-172) */
+int  vxrt_sync(VxrtHandle* h);
+int  vxrt_reset_accumulation(VxrtHandle* h);
+
+/* ---- output ------------------------------------------------------------------------- */
+/* replaces queue_present (pipeline.rs:237-254): the frame is a headless device buffer. */
+int  vxrt_read_output(VxrtHandle* h, uint8_t* rgba8, size_t nbytes);
+int  vxrt_read_buffer(VxrtHandle* h, int buffer_id, void* dst, size_t nbytes);
+size_t vxrt_buffer_bytes(const VxrtHandle* h, int buffer_id);
+void* vxrt_device_buffer(VxrtHandle* h, int buffer_id);     /* zero-copy consumers (NCCL gather) */
+void* vxrt_cuda_stream(VxrtHandle* h);                      /* cudaStream_t of the handle         */
+int  vxrt_frame_stats(VxrtHandle* h, VxrtFrameStats* out);  /* syncs the stream                   */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

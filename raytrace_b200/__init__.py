@@ -1,0 +1,12 @@
+"""raytrace_b200 — B200-native voxel ray-tracing hot path (libvxrt) and the host-side mirror of the
+reference's `render` module interface.  Importing this package loads raytrace_b200/libvxrt.so; if the
+CUDA library has not been built the import fails (there is no fallback)."""
+from . import _native  # noqa: F401  (loads libvxrt.so, raises if missing)
+from .render import (Camera, Material, MATERIALS, Pipeline, Renderer, VxrtError, constants, create_instance,
+                     compute_triple_euler_vector, fill_uniform_data, load_materials_csv)
+from .game import Game
+from .world import ChunkStorage, PackedChunkData
+
+__all__ = ["Camera", "Material", "MATERIALS", "Pipeline", "Renderer", "VxrtError", "constants", "create_instance",
+           "compute_triple_euler_vector", "fill_uniform_data", "load_materials_csv", "Game", "ChunkStorage",
+           "PackedChunkData"]

@@ -1,0 +1,512 @@
+// api.cu — the extern "C" boundary of libvxrt (include/vxrt.h): handle life cycle, world upload,
+// frame parameters, the per-frame launch sequence and read-back.  Replaces the dispatch code of
+// src/render/pipeline/{pipeline.rs,render_data.rs,terrain_upload.rs} (reference).
+// No CPU fallback lives here: every compute entry point launches CUDA kernels or fails.
+#include "vxrt_internal.h"
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+#include <new>
+
+namespace {
+
+std::string g_create_error;
+
+#define CU(call)                                                                              \
+    do {                                                                                      \
+        cudaError_t e_ = (call);                                                              \
+        if (e_ != cudaSuccess) {                                                              \
+            h->err = std::string(#call) + ": " + cudaGetErrorString(e_);                      \
+            return VXRT_ERR_CUDA;                                                             \
+        }                                                                                     \
+    } while (0)
+
+int fail(VxrtHandle* h, int code, const char* msg) { h->err = msg; return code; }
+
+bool pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
+int ilog2(int v) { int l = 0; while ((1 << l) < v) l++; return l; }
+
+// pipeline.rs:103 — dilation of each of the six bilateral passes
+const int kDenoiseSizes[6] = {1, 2, 4, 8, 8, 16};
+
+// host-side fp32 helpers; this file is compiled with -ffp-contract=off so each operator is one rounding
+struct H3 { float x, y, z; };
+float hmix(float a, float b, float t) { return a * (1.0f - t) + b * t; }
+
+// raytrace.comp:317-318: per-frame constants evaluated once (cos/sin in double, rounded once — the
+// same rule the oracle uses, oracle/vxrt_oracle_trace.cpp orc_trace)
+void sun_constants(float sun_angle, H3* dir, H3* light) {
+    const float ca = (float)cos((double)sun_angle), sa = (float)sin((double)sun_angle);
+    H3 v = {ca * 0.5f + (sun_angle - 0.5f) * 0.5f, sa, ca};
+    const float l = sqrtf((v.x * v.x + v.y * v.y) + v.z * v.z);
+    dir->x = v.x / l; dir->y = v.y / l; dir->z = v.z / l;
+    // sun_color, raytrace.comp:259-269
+    const float horizon = sqrtf(dir->x * dir->x + dir->y * dir->y);
+    const float sun_amount = fminf(1.0f - horizon, 0.02f) * 50.0f;
+    const H3 main_color = {0.9647f * 2.0f, 0.7843f * 2.0f, 0.8824f * 2.0f};
+    const H3 sunset = {0.7412f * 2.0f, 0.2157f * 2.0f, 0.1686f * 2.0f};
+    if (dir->z >= 0.0f) {
+        light->x = hmix(sunset.x, main_color.x, sun_amount); light->y = hmix(sunset.y, main_color.y, sun_amount);
+        light->z = hmix(sunset.z, main_color.z, sun_amount);
+    } else {
+        const float t = sun_amount * 2.0f;
+        light->x = hmix(sunset.x, 0.0f, t); light->y = hmix(sunset.y, 0.0f, t); light->z = hmix(sunset.z, 0.0f, t);
+    }
+}
+
+// raytrace.comp:190-197 as 256-entry tables (noise channels are 8 bit); same rule as orc_diffuse_luts
+void diffuse_luts(float* lut) {
+    const float PI = 3.1415926535897932384626433832795f;
+    for (int b = 0; b < 256; b++) {
+        const float n = (float)b / 255.0f;
+        const float theta1 = PI * 2.0f * n;
+        const float theta2 = (float)acos((double)(1.0f - 2.0f * n));
+        lut[b] = (float)sin((double)theta1);
+        lut[256 + b] = (float)cos((double)theta1);
+        lut[512 + b] = (float)sin((double)theta2);
+        lut[768 + b] = (float)cos((double)theta2);
+    }
+}
+
+size_t pixels(const VxrtHandle* h) { return (size_t)h->cfg.width * h->cfg.height; }
+size_t voxels(const VxrtHandle* h) { return (size_t)h->cfg.nx * h->cfg.ny * h->cfg.nz; }
+
+struct BufDesc { void* ptr; size_t bytes; };
+BufDesc buffer_of(const VxrtHandle* h, int id) {
+    const size_t P = pixels(h);
+    switch (id) {
+        case VXRT_BUF_OUTPUT: return {h->d_output, P * 4};
+        case VXRT_BUF_LIGHTING: return {h->d_lighting, P * 8};
+        case VXRT_BUF_DEPTH: return {h->d_depth, P * 2};
+        case VXRT_BUF_NORMAL: return {h->d_normal, P};
+        case VXRT_BUF_ALBEDO: return {h->d_albedo, P * 4};
+        case VXRT_BUF_EMISSION: return {h->d_emission, P * 4};
+        case VXRT_BUF_FOG: return {h->d_fog, P * 4};
+        case VXRT_BUF_HIT_VOXEL: return {h->d_hit_voxel, h->d_hit_voxel ? P * 12 : 0};
+        case VXRT_BUF_HIT_FACE: return {h->d_hit_face, h->d_hit_face ? P : 0};
+        case VXRT_BUF_HIT_WORD: return {h->d_hit_word, h->d_hit_word ? P * 4 : 0};
+        case VXRT_BUF_HIT_T: return {h->d_hit_t, h->d_hit_t ? P * 4 : 0};
+        case VXRT_BUF_STEPS: return {h->d_steps, h->d_steps ? P * 4 : 0};
+        case VXRT_BUF_RAYS: return {h->d_rays, h->d_rays ? P : 0};
+        case VXRT_BUF_ACCUM: return {h->d_accum, h->d_accum ? P * 16 : 0};
+        case VXRT_BUF_LIGHTING_RAW: return {h->d_lighting_raw, h->d_lighting_raw ? P * 8 : 0};
+        default: return {nullptr, 0};
+    }
+}
+
+int alloc_zero(VxrtHandle* h, void** p, size_t bytes) {
+    CU(cudaMalloc(p, bytes));
+    CU(cudaMemsetAsync(*p, 0, bytes, h->stream));
+    return VXRT_OK;
+}
+
+// 3-D box copy host -> window (both x fastest).  Box extents (ex,ey,ez) at texel (x0,y0,z0).
+template <typename T>
+int upload_box(VxrtHandle* h, T* d_base, const T* src, int x0, int y0, int z0, int ex, int ey, int ez) {
+    cudaMemcpy3DParms p;
+    memset(&p, 0, sizeof p);
+    p.srcPtr = make_cudaPitchedPtr(const_cast<T*>(src), (size_t)ex * sizeof(T), (size_t)ex, (size_t)ey);
+    p.dstPtr = make_cudaPitchedPtr(d_base, (size_t)h->cfg.nx * sizeof(T), (size_t)h->cfg.nx, (size_t)h->cfg.ny);
+    p.dstPos = make_cudaPos((size_t)x0 * sizeof(T), (size_t)y0, (size_t)z0);
+    p.extent = make_cudaExtent((size_t)ex * sizeof(T), (size_t)ey, (size_t)ez);
+    p.kind = cudaMemcpyHostToDevice;
+    CU(cudaMemcpy3DAsync(&p, h->stream));
+    return VXRT_OK;
+}
+
+int mark_dirty_box(VxrtHandle* h, int x0, int y0, int z0, int ex, int ey, int ez) {
+    // host-side list of chunks to rebuild, pushed as flags
+    const int cxn = h->cfg.nx >> 6, cyn = h->cfg.ny >> 6, czn = h->cfg.nz >> 6;
+    std::string flags((size_t)cxn * cyn * czn * 4, '\0');
+    uint32_t* f = reinterpret_cast<uint32_t*>(&flags[0]);
+    for (int cz = z0 >> 6; cz <= (z0 + ez - 1) >> 6; cz++)
+        for (int cy = y0 >> 6; cy <= (y0 + ey - 1) >> 6; cy++)
+            for (int cx = x0 >> 6; cx <= (x0 + ex - 1) >> 6; cx++) f[(cz * cyn + cy) * cxn + cx] = 1u;
+    CU(cudaMemcpyAsync(h->d_dirty, f, flags.size(), cudaMemcpyHostToDevice, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return VXRT_OK;
+}
+
+int rebuild_dirty(VxrtHandle* h) {
+    CU(vxrt_launch_build_minefield(h->d_materials, h->d_minefield, h->cfg.nx, h->cfg.ny, h->cfg.nz, h->d_dirty, h->stream));
+    CU(cudaMemsetAsync(h->d_dirty, 0, (size_t)(h->cfg.nx >> 6) * (h->cfg.ny >> 6) * (h->cfg.nz >> 6) * 4, h->stream));
+    return VXRT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int vxrt_abi_version(void) { return VXRT_ABI_VERSION; }
+
+const char* vxrt_last_error(const VxrtHandle* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+int vxrt_create(const VxrtConfig* cfg, VxrtHandle** out) {
+    if (!out) { g_create_error = "vxrt_create: out is NULL"; return VXRT_ERR_INVALID; }
+    *out = nullptr;
+    if (!cfg) { g_create_error = "vxrt_create: cfg is NULL"; return VXRT_ERR_INVALID; }
+    if (cfg->abi_version != VXRT_ABI_VERSION) { g_create_error = "vxrt_create: abi_version mismatch"; return VXRT_ERR_INVALID; }
+    if (cfg->width <= 0 || cfg->height <= 0 || cfg->width > 32768 || cfg->height > 32768) {
+        g_create_error = "vxrt_create: bad frame size"; return VXRT_ERR_INVALID;
+    }
+    if (!pow2(cfg->nx) || !pow2(cfg->ny) || !pow2(cfg->nz) || cfg->nx < 64 || cfg->ny < 64 || cfg->nz < 64 ||
+        cfg->nx > 4096 || cfg->ny > 4096 || cfg->nz > 4096) {
+        g_create_error = "vxrt_create: window dims must be powers of two in [64, 4096]"; return VXRT_ERR_INVALID;
+    }
+    if (cfg->mode < VXRT_MODE_PRIMARY || cfg->mode > VXRT_MODE_FULL) { g_create_error = "vxrt_create: bad mode"; return VXRT_ERR_INVALID; }
+    if (cfg->max_steps < 0) { g_create_error = "vxrt_create: max_steps < 0"; return VXRT_ERR_INVALID; }
+    int row0 = cfg->row_begin, row1 = cfg->row_end;
+    if (row0 == 0 && row1 == 0) row1 = cfg->height;
+    if (row0 < 0 || row1 > cfg->height || row0 >= row1) { g_create_error = "vxrt_create: bad row band"; return VXRT_ERR_INVALID; }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        g_create_error = std::string("vxrt_create: no CUDA device (there is no CPU fallback): ") + cudaGetErrorString(e);
+        return VXRT_ERR_CUDA;
+    }
+    if (cfg->device < 0 || cfg->device >= ndev) { g_create_error = "vxrt_create: device ordinal out of range"; return VXRT_ERR_INVALID; }
+    e = cudaSetDevice(cfg->device);
+    if (e != cudaSuccess) { g_create_error = std::string("cudaSetDevice: ") + cudaGetErrorString(e); return VXRT_ERR_CUDA; }
+
+    VxrtHandle* h = new (std::nothrow) VxrtHandle();
+    if (!h) { g_create_error = "vxrt_create: out of host memory"; return VXRT_ERR_INVALID; }
+    h->cfg = *cfg;
+    if (h->cfg.max_steps == 0) h->cfg.max_steps = 2048;      // raytrace.comp:109
+    h->row0 = row0; h->row1 = row1;
+    // denoise needs 3*size rows of context per pass (bilateral_denoise.comp taps reach +-3*size)
+    int halo = 0;
+    if (cfg->flags & VXRT_FLAG_DENOISE) for (int k = 0; k < 6; k++) halo += 3 * kDenoiseSizes[k];
+    h->trace_row0 = row0 - halo < 0 ? 0 : row0 - halo;
+    h->trace_row1 = row1 + halo > cfg->height ? cfg->height : row1 + halo;
+    h->stream = nullptr;
+    for (int i = 0; i < 5; i++) h->ev[i] = nullptr;
+    h->d_materials = nullptr; h->d_minefield = nullptr; h->d_noise = nullptr; h->d_lut = nullptr; h->d_dirty = nullptr;
+    h->d_edits = nullptr; h->edits_cap = 0;
+    h->d_lighting = h->d_pong = h->d_lighting_raw = nullptr;
+    h->d_depth = nullptr; h->d_normal = nullptr; h->d_albedo = h->d_emission = h->d_fog = h->d_output = nullptr;
+    h->d_hit_voxel = nullptr; h->d_hit_face = nullptr; h->d_hit_word = nullptr; h->d_hit_t = nullptr; h->d_steps = nullptr;
+    h->d_rays = nullptr; h->d_accum = nullptr; h->d_counters = nullptr;
+    h->have_frame = h->have_world = h->have_noise = h->rendered = false;
+    h->frames_accumulated = 0;
+    memset(&h->frame, 0, sizeof h->frame);
+    h->h_noise.assign((size_t)VXRT_NOISE_SIZE * VXRT_NOISE_SIZE * 4, 0);
+
+    auto init = [&]() -> int {
+        CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+        for (int i = 0; i < 5; i++) CU(cudaEventCreate(&h->ev[i]));
+        const size_t V = voxels(h), P = pixels(h);
+        int rc;
+        if ((rc = alloc_zero(h, (void**)&h->d_materials, V * 4))) return rc;
+        if ((rc = alloc_zero(h, (void**)&h->d_minefield, V))) return rc;
+        if ((rc = alloc_zero(h, (void**)&h->d_noise, h->h_noise.size()))) return rc;
+        if ((rc = alloc_zero(h, (void**)&h->d_dirty, (size_t)(cfg->nx >> 6) * (cfg->ny >> 6) * (cfg->nz >> 6) * 4))) return rc;
+        if ((rc = alloc_zero(h, (void**)&h->d_counters, 8 * sizeof(unsigned long long)))) return rc;
+        CU(cudaMalloc((void**)&h->d_lut, 1024 * sizeof(float)));
+        float lut[1024];
+        diffuse_luts(lut);
+        CU(cudaMemcpyAsync(h->d_lut, lut, sizeof lut, cudaMemcpyHostToDevice, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+        if ((rc = alloc_zero(h, (void**)&h->d_lighting, P * 8))) return rc;
+        if ((rc = alloc_zero(h, (void**)&h->d_depth, P * 2))) return rc;
+        if ((rc = alloc_zero(h, (void**)&h->d_normal, P))) return rc;
+        if ((rc = alloc_zero(h, (void**)&h->d_albedo, P * 4))) return rc;
+        if ((rc = alloc_zero(h, (void**)&h->d_emission, P * 4))) return rc;
+        if ((rc = alloc_zero(h, (void**)&h->d_fog, P * 4))) return rc;
+        if ((rc = alloc_zero(h, (void**)&h->d_output, P * 4))) return rc;
+        if (cfg->flags & VXRT_FLAG_DENOISE) if ((rc = alloc_zero(h, (void**)&h->d_pong, P * 8))) return rc;
+        if (cfg->flags & VXRT_FLAG_HIT_BUFFERS) {
+            if ((rc = alloc_zero(h, (void**)&h->d_hit_voxel, P * 12))) return rc;
+            if ((rc = alloc_zero(h, (void**)&h->d_hit_face, P))) return rc;
+            if ((rc = alloc_zero(h, (void**)&h->d_hit_word, P * 4))) return rc;
+            if ((rc = alloc_zero(h, (void**)&h->d_hit_t, P * 4))) return rc;
+            if ((rc = alloc_zero(h, (void**)&h->d_steps, P * 4))) return rc;
+            if ((rc = alloc_zero(h, (void**)&h->d_rays, P))) return rc;
+            if ((rc = alloc_zero(h, (void**)&h->d_lighting_raw, P * 8))) return rc;
+        }
+        if (cfg->flags & VXRT_FLAG_ACCUMULATE) if ((rc = alloc_zero(h, (void**)&h->d_accum, P * 16))) return rc;
+        CU(cudaStreamSynchronize(h->stream));
+        return VXRT_OK;
+    };
+    const int rc = init();
+    if (rc != VXRT_OK) { g_create_error = h->err; vxrt_destroy(h); return rc; }
+    *out = h;
+    return VXRT_OK;
+}
+
+void vxrt_destroy(VxrtHandle* h) {
+    if (!h) return;
+    cudaSetDevice(h->cfg.device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    void* ptrs[] = {h->d_materials, h->d_minefield, h->d_noise, h->d_lut, h->d_dirty, h->d_edits, h->d_lighting, h->d_pong,
+                    h->d_lighting_raw, h->d_depth, h->d_normal, h->d_albedo, h->d_emission, h->d_fog, h->d_output,
+                    h->d_hit_voxel, h->d_hit_face, h->d_hit_word, h->d_hit_t, h->d_steps, h->d_rays, h->d_accum, h->d_counters};
+    for (void* p : ptrs) if (p) cudaFree(p);
+    for (int i = 0; i < 5; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+// ---- world ------------------------------------------------------------------------------------
+
+int vxrt_upload_chunk(VxrtHandle* h, int cx, int cy, int cz, const uint32_t* materials, const uint8_t* minefield) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (!materials) return fail(h, VXRT_ERR_INVALID, "vxrt_upload_chunk: materials is NULL");
+    if (cx < 0 || cy < 0 || cz < 0 || cx >= (h->cfg.nx >> 6) || cy >= (h->cfg.ny >> 6) || cz >= (h->cfg.nz >> 6))
+        return fail(h, VXRT_ERR_INVALID, "vxrt_upload_chunk: chunk coordinate outside the window");
+    CU(cudaSetDevice(h->cfg.device));
+    int rc;
+    if ((rc = upload_box(h, h->d_materials, materials, cx * 64, cy * 64, cz * 64, 64, 64, 64))) return rc;
+    if (minefield) {
+        if ((rc = upload_box(h, h->d_minefield, minefield, cx * 64, cy * 64, cz * 64, 64, 64, 64))) return rc;
+    } else {
+        if ((rc = mark_dirty_box(h, cx * 64, cy * 64, cz * 64, 64, 64, 64))) return rc;
+        if ((rc = rebuild_dirty(h))) return rc;
+    }
+    CU(cudaStreamSynchronize(h->stream));     // caller may free its buffers on return
+    h->have_world = true;
+    return VXRT_OK;
+}
+
+int vxrt_upload_world(VxrtHandle* h, const uint32_t* materials, const uint8_t* minefield) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (!materials) return fail(h, VXRT_ERR_INVALID, "vxrt_upload_world: materials is NULL");
+    CU(cudaSetDevice(h->cfg.device));
+    const size_t V = voxels(h);
+    CU(cudaMemcpyAsync(h->d_materials, materials, V * 4, cudaMemcpyHostToDevice, h->stream));
+    if (minefield) CU(cudaMemcpyAsync(h->d_minefield, minefield, V, cudaMemcpyHostToDevice, h->stream));
+    else CU(vxrt_launch_build_minefield(h->d_materials, h->d_minefield, h->cfg.nx, h->cfg.ny, h->cfg.nz, nullptr, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    h->have_world = true;
+    return VXRT_OK;
+}
+
+int vxrt_upload_slice(VxrtHandle* h, int axis, int offset, const uint32_t* materials, const uint8_t* minefield) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (!materials) return fail(h, VXRT_ERR_INVALID, "vxrt_upload_slice: materials is NULL");
+    if (axis < 0 || axis > 2) return fail(h, VXRT_ERR_INVALID, "vxrt_upload_slice: axis must be 0, 1 or 2");
+    const int dims[3] = {h->cfg.nx, h->cfg.ny, h->cfg.nz};
+    if (offset < 0 || offset % 16 != 0 || offset + 16 > dims[axis])
+        return fail(h, VXRT_ERR_INVALID, "vxrt_upload_slice: offset must be a multiple of 16 inside the window");
+    int e[3] = {dims[0], dims[1], dims[2]}, o[3] = {0, 0, 0};
+    e[axis] = 16; o[axis] = offset;                           // constants.rs:30 SLICE_SIZE
+    CU(cudaSetDevice(h->cfg.device));
+    int rc;
+    if ((rc = upload_box(h, h->d_materials, materials, o[0], o[1], o[2], e[0], e[1], e[2]))) return rc;
+    if (minefield) {
+        if ((rc = upload_box(h, h->d_minefield, minefield, o[0], o[1], o[2], e[0], e[1], e[2]))) return rc;
+    } else {
+        if ((rc = mark_dirty_box(h, o[0], o[1], o[2], e[0], e[1], e[2]))) return rc;
+        if ((rc = rebuild_dirty(h))) return rc;
+    }
+    CU(cudaStreamSynchronize(h->stream));
+    h->have_world = true;
+    return VXRT_OK;
+}
+
+int vxrt_generate_world(VxrtHandle* h, int kind, uint32_t seed) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (kind < 0 || kind > 1) return fail(h, VXRT_ERR_INVALID, "vxrt_generate_world: kind must be 0 (heightmap) or 1 (biome)");
+    CU(cudaSetDevice(h->cfg.device));
+    CU(vxrt_launch_generate(h->d_materials, h->cfg.nx, h->cfg.ny, h->cfg.nz, kind, seed, h->stream));
+    CU(vxrt_launch_build_minefield(h->d_materials, h->d_minefield, h->cfg.nx, h->cfg.ny, h->cfg.nz, nullptr, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    h->have_world = true;
+    return VXRT_OK;
+}
+
+int vxrt_rebuild_minefield(VxrtHandle* h) {
+    if (!h) return VXRT_ERR_INVALID;
+    CU(cudaSetDevice(h->cfg.device));
+    CU(vxrt_launch_build_minefield(h->d_materials, h->d_minefield, h->cfg.nx, h->cfg.ny, h->cfg.nz, nullptr, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return VXRT_OK;
+}
+
+int vxrt_read_world(VxrtHandle* h, uint32_t* materials, uint8_t* minefield) {
+    if (!h) return VXRT_ERR_INVALID;
+    CU(cudaSetDevice(h->cfg.device));
+    const size_t V = voxels(h);
+    if (materials) CU(cudaMemcpyAsync(materials, h->d_materials, V * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (minefield) CU(cudaMemcpyAsync(minefield, h->d_minefield, V, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return VXRT_OK;
+}
+
+int vxrt_upload_blue_noise(VxrtHandle* h, const uint8_t* rgba, size_t nbytes) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (!rgba) return fail(h, VXRT_ERR_INVALID, "vxrt_upload_blue_noise: rgba is NULL");
+    if (nbytes != h->h_noise.size()) return fail(h, VXRT_ERR_SIZE, "vxrt_upload_blue_noise: expected 512*512*4 bytes");
+    CU(cudaSetDevice(h->cfg.device));
+    memcpy(h->h_noise.data(), rgba, nbytes);
+    CU(cudaMemcpyAsync(h->d_noise, h->h_noise.data(), nbytes, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    h->have_noise = true;
+    return VXRT_OK;
+}
+
+// ---- edits ------------------------------------------------------------------------------------
+
+int vxrt_apply_edits_device(VxrtHandle* h, const void* d_edits, size_t n) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (n && !d_edits) return fail(h, VXRT_ERR_INVALID, "vxrt_apply_edits_device: d_edits is NULL");
+    if (!h->have_world) return fail(h, VXRT_ERR_STATE, "vxrt_apply_edits: no world uploaded");
+    if (n == 0) return VXRT_OK;
+    CU(cudaSetDevice(h->cfg.device));
+    CU(vxrt_launch_apply_edits(h->d_materials, h->d_dirty, (const VxrtEdit*)d_edits, n, h->cfg.nx, h->cfg.ny, h->cfg.nz, h->stream));
+    return rebuild_dirty(h);
+}
+
+int vxrt_apply_edits(VxrtHandle* h, const VxrtEdit* edits, size_t n) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (n && !edits) return fail(h, VXRT_ERR_INVALID, "vxrt_apply_edits: edits is NULL");
+    if (!h->have_world) return fail(h, VXRT_ERR_STATE, "vxrt_apply_edits: no world uploaded");
+    if (n == 0) return VXRT_OK;
+    CU(cudaSetDevice(h->cfg.device));
+    if (n > h->edits_cap) {
+        if (h->d_edits) CU(cudaFree(h->d_edits));
+        h->d_edits = nullptr; h->edits_cap = 0;
+        size_t cap = 1024; while (cap < n) cap *= 2;
+        CU(cudaMalloc(&h->d_edits, cap * sizeof(VxrtEdit)));
+        h->edits_cap = cap;
+    }
+    CU(cudaMemcpyAsync(h->d_edits, edits, n * sizeof(VxrtEdit), cudaMemcpyHostToDevice, h->stream));
+    const int rc = vxrt_apply_edits_device(h, h->d_edits, n);
+    if (rc) return rc;
+    CU(cudaStreamSynchronize(h->stream));    // the host list may be reused on return
+    return VXRT_OK;
+}
+
+// ---- per frame --------------------------------------------------------------------------------
+
+int vxrt_set_frame(VxrtHandle* h, const VxrtFrameParams* p) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (!p) return fail(h, VXRT_ERR_INVALID, "vxrt_set_frame: params is NULL");
+    h->frame = *p;
+    h->have_frame = true;
+    return VXRT_OK;
+}
+
+int vxrt_reset_accumulation(VxrtHandle* h) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (!h->d_accum) return fail(h, VXRT_ERR_STATE, "vxrt_reset_accumulation: handle created without VXRT_FLAG_ACCUMULATE");
+    CU(cudaSetDevice(h->cfg.device));
+    CU(cudaMemsetAsync(h->d_accum, 0, pixels(h) * 16, h->stream));
+    h->frames_accumulated = 0;
+    return VXRT_OK;
+}
+
+int vxrt_render_frame(VxrtHandle* h) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (!h->have_world) return fail(h, VXRT_ERR_STATE, "vxrt_render_frame: no world uploaded");
+    if (!h->have_noise) return fail(h, VXRT_ERR_STATE, "vxrt_render_frame: no blue noise uploaded");
+    if (!h->have_frame) return fail(h, VXRT_ERR_STATE, "vxrt_render_frame: vxrt_set_frame not called");
+    CU(cudaSetDevice(h->cfg.device));
+    const VxrtFrameParams& f = h->frame;
+    TraceParams P;
+    memset(&P, 0, sizeof P);
+    P.ox = f.origin[0]; P.oy = f.origin[1]; P.oz = f.origin[2];
+    P.fx = f.forward[0]; P.fy = f.forward[1]; P.fz = f.forward[2];
+    P.ux = f.up[0]; P.uy = f.up[1]; P.uz = f.up[2];
+    P.rx = f.right[0]; P.ry = f.right[1]; P.rz = f.right[2];
+    P.lrx = (float)f.rotation[0]; P.lry = (float)f.rotation[1]; P.lrz = (float)f.rotation[2];   // raytrace.comp:104
+    H3 sd, sl;
+    sun_constants(f.sun_angle, &sd, &sl);
+    P.sun_x = sd.x; P.sun_y = sd.y; P.sun_z = sd.z; P.sl_r = sl.x; P.sl_g = sl.y; P.sl_b = sl.z;
+    {   // raytrace.comp:298-303: texel (seed % 512, seed / 512), clamp-to-edge (render_data.rs:110-128)
+        uint32_t ix = f.seed % VXRT_NOISE_SIZE, iy = f.seed / VXRT_NOISE_SIZE;
+        if (iy > VXRT_NOISE_SIZE - 1) iy = VXRT_NOISE_SIZE - 1;
+        const uint8_t* t = h->h_noise.data() + ((size_t)iy * VXRT_NOISE_SIZE + ix) * 4;
+        P.noise_base_x = ((float)t[0] / 255.0f) * 255.0f;
+        P.noise_base_y = ((float)t[1] / 255.0f) * 255.0f;
+    }
+    P.width = h->cfg.width; P.height = h->cfg.height; P.row0 = h->trace_row0; P.row1 = h->trace_row1;
+    P.nx = h->cfg.nx; P.ny = h->cfg.ny; P.nz = h->cfg.nz;
+    P.lx = ilog2(P.nx); P.ly = ilog2(P.ny); P.lz = ilog2(P.nz);
+    P.hx = (float)(P.nx / 2); P.hy = (float)(P.ny / 2); P.hz = (float)(P.nz / 2);
+    P.max_steps = h->cfg.max_steps; P.mode = h->cfg.mode; P.flags = h->cfg.flags;
+    P.minefield = h->d_minefield; P.materials = h->d_materials; P.noise = h->d_noise; P.lut = h->d_lut;
+    P.lighting = h->d_lighting; P.depth = h->d_depth; P.normal = h->d_normal; P.albedo = h->d_albedo;
+    P.emission = h->d_emission; P.fog = h->d_fog;
+    P.hit_voxel = h->d_hit_voxel; P.hit_face = h->d_hit_face; P.hit_word = h->d_hit_word; P.hit_t = h->d_hit_t;
+    P.steps = h->d_steps; P.rays = h->d_rays;
+    P.accum = h->d_accum;
+    P.counters = h->d_counters;
+
+    CU(cudaMemsetAsync(h->d_counters, 0, 8 * sizeof(unsigned long long), h->stream));
+    CU(cudaEventRecord(h->ev[0], h->stream));
+    CU(vxrt_launch_trace(P, h->stream));
+    CU(cudaEventRecord(h->ev[1], h->stream));
+    if (h->d_lighting_raw)
+        CU(cudaMemcpyAsync(h->d_lighting_raw, h->d_lighting, pixels(h) * 8, cudaMemcpyDeviceToDevice, h->stream));
+    if (h->d_accum) h->frames_accumulated++;
+    if (h->cfg.flags & VXRT_FLAG_DENOISE) {
+        // pipeline.rs:98-115: even passes lighting -> pong, odd passes pong -> lighting.  A band shrinks
+        // by 3*size rows per pass towards [row0,row1) so that only valid rows are ever read.
+        int remaining = 0;
+        for (int k = 0; k < 6; k++) remaining += 3 * kDenoiseSizes[k];
+        for (int k = 0; k < 6; k++) {
+            remaining -= 3 * kDenoiseSizes[k];
+            int r0 = h->row0 - remaining, r1 = h->row1 + remaining;
+            if (r0 < 0) r0 = 0;
+            if (r1 > h->cfg.height) r1 = h->cfg.height;
+            const bool odd = (k & 1) != 0;
+            const int swap = (odd && (h->cfg.flags & VXRT_FLAG_PONG_SWAP)) ? 1 : 0;
+            CU(vxrt_launch_denoise(odd ? h->d_pong : h->d_lighting, odd ? h->d_lighting : h->d_pong, h->d_depth, h->d_normal,
+                                   h->cfg.width, h->cfg.height, kDenoiseSizes[k], swap, r0, r1, h->stream));
+        }
+    }
+    CU(cudaEventRecord(h->ev[2], h->stream));
+    if (h->cfg.flags & VXRT_FLAG_FINALIZE)
+        CU(vxrt_launch_finalize(h->d_albedo, h->d_emission, h->d_fog, h->d_lighting, h->d_depth, h->d_noise, h->d_output,
+                                h->cfg.width, h->cfg.height, h->row0, h->row1, h->stream));
+    CU(cudaEventRecord(h->ev[3], h->stream));
+    h->rendered = true;
+    return VXRT_OK;
+}
+
+int vxrt_sync(VxrtHandle* h) {
+    if (!h) return VXRT_ERR_INVALID;
+    CU(cudaSetDevice(h->cfg.device));
+    CU(cudaStreamSynchronize(h->stream));
+    return VXRT_OK;
+}
+
+// ---- output -----------------------------------------------------------------------------------
+
+size_t vxrt_buffer_bytes(const VxrtHandle* h, int buffer_id) { return h ? buffer_of(h, buffer_id).bytes : 0; }
+
+void* vxrt_device_buffer(VxrtHandle* h, int buffer_id) { return h ? buffer_of(h, buffer_id).ptr : nullptr; }
+
+void* vxrt_cuda_stream(VxrtHandle* h) { return h ? (void*)h->stream : nullptr; }
+
+int vxrt_read_buffer(VxrtHandle* h, int buffer_id, void* dst, size_t nbytes) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (!dst) return fail(h, VXRT_ERR_INVALID, "vxrt_read_buffer: dst is NULL");
+    const BufDesc b = buffer_of(h, buffer_id);
+    if (!b.ptr) return fail(h, VXRT_ERR_STATE, "vxrt_read_buffer: buffer not allocated for this handle (check the create flags)");
+    if (nbytes < b.bytes) return fail(h, VXRT_ERR_SIZE, "vxrt_read_buffer: host buffer too small");
+    CU(cudaSetDevice(h->cfg.device));
+    CU(cudaMemcpyAsync(dst, b.ptr, b.bytes, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return VXRT_OK;
+}
+
+int vxrt_read_output(VxrtHandle* h, uint8_t* rgba8, size_t nbytes) { return vxrt_read_buffer(h, VXRT_BUF_OUTPUT, rgba8, nbytes); }
+
+int vxrt_frame_stats(VxrtHandle* h, VxrtFrameStats* out) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (!out) return fail(h, VXRT_ERR_INVALID, "vxrt_frame_stats: out is NULL");
+    if (!h->rendered) return fail(h, VXRT_ERR_STATE, "vxrt_frame_stats: no frame rendered yet");
+    CU(cudaSetDevice(h->cfg.device));
+    unsigned long long c[8];
+    CU(cudaMemcpyAsync(c, h->d_counters, sizeof c, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    out->rays = c[0]; out->steps = c[1]; out->hits = c[2]; out->noise_fetches = c[3]; out->limit_exhausted = c[4];
+    CU(cudaEventElapsedTime(&out->trace_ms, h->ev[0], h->ev[1]));
+    CU(cudaEventElapsedTime(&out->denoise_ms, h->ev[1], h->ev[2]));
+    CU(cudaEventElapsedTime(&out->finalize_ms, h->ev[2], h->ev[3]));
+    CU(cudaEventElapsedTime(&out->total_ms, h->ev[0], h->ev[3]));
+    return VXRT_OK;
+}
+
+}  // extern "C"

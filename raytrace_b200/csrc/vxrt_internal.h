@@ -1,0 +1,72 @@
+// vxrt_internal.h — handle layout and launch prototypes shared by the .cu files of libvxrt.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/vxrt.h"
+
+#define VXRT_NOISE_SIZE 512
+#define VXRT_CHUNK 64
+
+// Per-frame constants handed to the kernels by value (fits the 4 KB parameter space).
+struct TraceParams {
+    // frame block (structs.rs:3-31), decoded
+    float ox, oy, oz, fx, fy, fz, ux, uy, uz, rx, ry, rz;
+    float lrx, lry, lrz;                 // window centre as float (raytrace.comp:104)
+    float sun_x, sun_y, sun_z;           // raytrace.comp:317, evaluated once on the host
+    float sl_r, sl_g, sl_b;              // sun_color(), raytrace.comp:318
+    float noise_base_x, noise_base_y;    // raytrace.comp:302-303
+    // geometry
+    int width, height, row0, row1;       // rows [row0,row1) are traced
+    int nx, ny, nz;                      // window dims (powers of two)
+    int lx, ly, lz;                      // log2 of the dims
+    float hx, hy, hz;                    // half dims (pos_offset, raytrace.comp:105)
+    int max_steps, mode;
+    uint32_t flags;
+    float inv_frames;                    // accumulation: 1/(frames so far incl. this one) is NOT used; see k_trace
+    // device pointers
+    const uint8_t* minefield;            // linear [nz][ny][nx]
+    const uint32_t* materials;           // linear [nz][ny][nx]
+    const uint8_t* noise;                // 512*512*4
+    const float* lut;                    // 4*256: sin1, cos1, sin2, cos2 (raytrace.comp:190-197)
+    ushort4* lighting; uint16_t* depth; uint8_t* normal; uchar4* albedo; uchar4* emission; uchar4* fog;
+    int32_t* hit_voxel; uint8_t* hit_face; uint32_t* hit_word; float* hit_t; uint32_t* steps; uint8_t* rays;
+    float4* accum;
+    unsigned long long* counters;        // [0]=rays [1]=steps [2]=hits [3]=noise fetches [4]=limit exhausted
+};
+
+struct VxrtHandle {
+    VxrtConfig cfg;
+    int row0, row1;                      // rendered G-buffer rows
+    int trace_row0, trace_row1;          // rows traced (band + denoise halo)
+    cudaStream_t stream;
+    cudaEvent_t ev[5];
+    std::string err;
+    // world
+    uint32_t* d_materials; uint8_t* d_minefield; uint8_t* d_noise; float* d_lut;
+    std::vector<uint8_t> h_noise;        // host copy: the seed texel is read on the host (raytrace.comp:298-303)
+    uint32_t* d_dirty;                   // one flag per 64^3 chunk
+    void* d_edits; size_t edits_cap;
+    // frame images
+    ushort4 *d_lighting, *d_pong, *d_lighting_raw;
+    uint16_t* d_depth; uint8_t* d_normal; uchar4 *d_albedo, *d_emission, *d_fog, *d_output;
+    int32_t* d_hit_voxel; uint8_t* d_hit_face; uint32_t* d_hit_word; float* d_hit_t; uint32_t* d_steps; uint8_t* d_rays;
+    float4* d_accum;
+    unsigned long long* d_counters;
+    VxrtFrameParams frame; bool have_frame, have_world, have_noise, rendered;
+    uint32_t frames_accumulated;
+};
+
+// launchers (each returns the cudaGetLastError() of its launch)
+cudaError_t vxrt_launch_trace(const TraceParams& p, cudaStream_t s);
+cudaError_t vxrt_launch_denoise(const ushort4* src, ushort4* dst, const uint16_t* depth, const uint8_t* normal,
+                                int width, int height, int size, int swap, int row0, int row1, cudaStream_t s);
+cudaError_t vxrt_launch_finalize(const uchar4* albedo, const uchar4* emission, const uchar4* fog, const ushort4* lighting,
+                                 const uint16_t* depth, const uint8_t* noise, uchar4* out, int width, int height,
+                                 int row0, int row1, cudaStream_t s);
+cudaError_t vxrt_launch_build_minefield(uint32_t* materials, uint8_t* minefield, int nx, int ny, int nz,
+                                        const uint32_t* dirty /*NULL = all chunks*/, cudaStream_t s);
+cudaError_t vxrt_launch_apply_edits(uint32_t* materials, uint32_t* dirty, const VxrtEdit* d_edits, size_t n,
+                                    int nx, int ny, int nz, cudaStream_t s);
+cudaError_t vxrt_launch_generate(uint32_t* materials, int nx, int ny, int nz, int kind, uint32_t seed, cudaStream_t s);

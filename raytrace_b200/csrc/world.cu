@@ -1,0 +1,206 @@
+// world.cu — device-resident voxel window: occupancy-LOD ("minefield") build, voxel edits and the
+// seeded synthetic world generators.
+//   k_build_minefield  replaces UnpackedChunkData::pack_into (src/world/chunk.rs:125-184)
+//   k_apply_edits      no reference equivalent beyond set_block (chunk.rs:115-117)
+//   k_generate_*       replaces src/world/generate.rs for SYNTHETIC, SEEDED inputs (the reference
+//                      generator draws from thread_rng and is not reproducible)
+#include "vxrt_internal.h"
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------
+// pack_into: per 64^3 chunk, minefield = 0 for solid voxels (bit 15), else the smallest k in 1..6
+// whose 2^k-aligned cube contains a solid voxel; a wholly empty chunk becomes all 6 / words 0.
+// One 512-thread block per chunk; the six "any solid" levels live in shared memory as bytes.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(512) k_build_minefield(uint32_t* __restrict__ materials, uint8_t* __restrict__ minefield,
+                                                         int nx, int ny, int nz, const uint32_t* __restrict__ dirty) {
+    if (dirty && !dirty[blockIdx.x]) return;
+    __shared__ uint8_t l1[32 * 32 * 32];
+    __shared__ uint8_t l2[16 * 16 * 16];
+    __shared__ uint8_t l3[8 * 8 * 8];
+    __shared__ uint8_t l4[4 * 4 * 4];
+    __shared__ uint8_t l5[2 * 2 * 2];
+    __shared__ uint8_t l6[1];
+    const int cxn = nx >> 6, cyn = ny >> 6;
+    const int cx = blockIdx.x % cxn, cy = (blockIdx.x / cxn) % cyn, cz = blockIdx.x / (cxn * cyn);
+    const size_t base = ((size_t)(cz * 64) * ny + cy * 64) * nx + cx * 64;
+    const int tid = threadIdx.x;
+    for (int i = tid; i < 32 * 32 * 32 / 4; i += 512) reinterpret_cast<uint32_t*>(l1)[i] = 0;
+    for (int i = tid; i < 16 * 16 * 16 / 4; i += 512) reinterpret_cast<uint32_t*>(l2)[i] = 0;
+    if (tid < 128) reinterpret_cast<uint32_t*>(l3)[tid] = 0;
+    if (tid < 16) reinterpret_cast<uint32_t*>(l4)[tid] = 0;
+    if (tid < 8) l5[tid] = 0;
+    if (tid == 0) l6[0] = 0;
+    __syncthreads();
+    // level 1 straight from the words (x fastest -> coalesced 256 B rows)
+    for (int v = tid; v < 64 * 64 * 64; v += 512) {
+        const int x = v & 63, y = (v >> 6) & 63, z = v >> 12;
+        const uint32_t w = materials[base + ((size_t)z * ny + y) * nx + x];
+        if ((w >> 15) & 1u) l1[((z >> 1) * 32 + (y >> 1)) * 32 + (x >> 1)] = 1;
+    }
+    __syncthreads();
+    for (int c = tid; c < 16 * 16 * 16; c += 512) {
+        const int x = c & 15, y = (c >> 4) & 15, z = c >> 8;
+        uint8_t any = 0;
+        for (int k = 0; k < 8; k++) any |= l1[((2 * z + (k >> 2)) * 32 + 2 * y + ((k >> 1) & 1)) * 32 + 2 * x + (k & 1)];
+        l2[c] = any;
+    }
+    __syncthreads();
+    if (tid < 512) {
+        const int x = tid & 7, y = (tid >> 3) & 7, z = tid >> 6;
+        uint8_t any = 0;
+        for (int k = 0; k < 8; k++) any |= l2[((2 * z + (k >> 2)) * 16 + 2 * y + ((k >> 1) & 1)) * 16 + 2 * x + (k & 1)];
+        l3[tid] = any;
+    }
+    __syncthreads();
+    if (tid < 64) {
+        const int x = tid & 3, y = (tid >> 2) & 3, z = tid >> 4;
+        uint8_t any = 0;
+        for (int k = 0; k < 8; k++) any |= l3[((2 * z + (k >> 2)) * 8 + 2 * y + ((k >> 1) & 1)) * 8 + 2 * x + (k & 1)];
+        l4[tid] = any;
+    }
+    __syncthreads();
+    if (tid < 8) {
+        const int x = tid & 1, y = (tid >> 1) & 1, z = tid >> 2;
+        uint8_t any = 0;
+        for (int k = 0; k < 8; k++) any |= l4[((2 * z + (k >> 2)) * 4 + 2 * y + ((k >> 1) & 1)) * 4 + 2 * x + (k & 1)];
+        l5[tid] = any;
+    }
+    __syncthreads();
+    if (tid == 0) { uint8_t any = 0; for (int k = 0; k < 8; k++) any |= l5[k]; l6[0] = any; }
+    __syncthreads();
+    const bool empty = !l6[0];                                                  // chunk.rs:155-161
+    for (int v = tid; v < 64 * 64 * 64; v += 512) {
+        const int x = v & 63, y = (v >> 6) & 63, z = v >> 12;
+        const size_t gi = base + ((size_t)z * ny + y) * nx + x;
+        uint8_t mf;
+        if (empty) { materials[gi] = 0; mf = 6; }
+        else if ((materials[gi] >> 15) & 1u) mf = 0;
+        else if (l1[((z >> 1) * 32 + (y >> 1)) * 32 + (x >> 1)]) mf = 1;
+        else if (l2[((z >> 2) * 16 + (y >> 2)) * 16 + (x >> 2)]) mf = 2;
+        else if (l3[((z >> 3) * 8 + (y >> 3)) * 8 + (x >> 3)]) mf = 3;
+        else if (l4[((z >> 4) * 4 + (y >> 4)) * 4 + (x >> 4)]) mf = 4;
+        else if (l5[((z >> 5) * 2 + (y >> 5)) * 2 + (x >> 5)]) mf = 5;
+        else mf = 6;
+        minefield[gi] = mf;
+    }
+}
+
+// world coordinate -> window texel: (w + N/2) mod N (raytrace.comp:105-106)
+__global__ void k_apply_edits(uint32_t* __restrict__ materials, uint32_t* __restrict__ dirty, const VxrtEdit* __restrict__ edits,
+                              size_t n, int nx, int ny, int nz) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const VxrtEdit e = edits[i];
+    const uint32_t x = (uint32_t)(e.x + nx / 2) & (uint32_t)(nx - 1), y = (uint32_t)(e.y + ny / 2) & (uint32_t)(ny - 1),
+                   z = (uint32_t)(e.z + nz / 2) & (uint32_t)(nz - 1);
+    materials[((size_t)z * ny + y) * nx + x] = e.word;
+    dirty[((z >> 6) * (ny >> 6) + (y >> 6)) * (nx >> 6) + (x >> 6)] = 1u;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Seeded synthetic worlds (integer-only so that raytrace_b200/worldgen.py reproduces them bit for
+// bit on the CPU).  Spec: DESIGN.md §5.
+// ---------------------------------------------------------------------------------------------
+__host__ __device__ inline uint32_t mix32(uint32_t a) {
+    a ^= a >> 16; a *= 0x7feb352du; a ^= a >> 15; a *= 0x846ca68bu; a ^= a >> 16; return a;
+}
+__host__ __device__ inline uint32_t hash3(uint32_t x, uint32_t y, uint32_t z, uint32_t s) {
+    return mix32(x * 0x9E3779B1u ^ mix32(y * 0x85EBCA77u ^ mix32(z * 0xC2B2AE3Du ^ s)));
+}
+__device__ inline uint32_t vnoise(uint32_t x, uint32_t y, uint32_t o, uint32_t S, uint32_t seed) {
+    const uint32_t i = x / S, fx = x % S, j = y / S, fy = y % S;
+    const uint64_t S3 = (uint64_t)S * S * S;
+    const uint64_t wx = (uint64_t)fx * fx * (3 * S - 2 * fx), wy = (uint64_t)fy * fy * (3 * S - 2 * fy);
+    const uint64_t v00 = hash3(i, j, o, seed) >> 16, v10 = hash3(i + 1, j, o, seed) >> 16,
+                   v01 = hash3(i, j + 1, o, seed) >> 16, v11 = hash3(i + 1, j + 1, o, seed) >> 16;
+    const uint64_t a = (v00 * (S3 - wx) + v10 * wx) / S3, b = (v01 * (S3 - wx) + v11 * wx) / S3;
+    return (uint32_t)((a * (S3 - wy) + b * wy) / S3);
+}
+
+struct GenParams { int nx, ny, nz, kind; uint32_t seed; uint32_t words[7]; int sx[64], sy[64], stype[64], samp[64]; };
+
+__device__ inline void biome_of(const GenParams& G, int x, int y, int* type, int* amp8) {
+    if (G.kind == 0) { *type = 0; *amp8 = 8; return; }
+    long long best = -1; int bk = 0;
+    for (int k = 0; k < 64; k++) {
+        const long long dx = x - G.sx[k], dy = y - G.sy[k], d = dx * dx + dy * dy;
+        if (best < 0 || d < best) { best = d; bk = k; }
+    }
+    *type = G.stype[bk]; *amp8 = G.samp[bk];
+}
+__device__ inline int column_height(const GenParams& G, int x, int y, int* type) {
+    int amp8; biome_of(G, x, y, type, &amp8);
+    const uint32_t S0 = (uint32_t)min(128, G.nx / 2);
+    const uint32_t amp = (uint32_t)(G.nz * 3 / 8);
+    uint32_t h = (uint32_t)(G.nz / 16);
+    uint32_t sum = 0;
+    for (uint32_t o = 0; o < 4; o++) sum += ((amp >> o) * vnoise((uint32_t)x, (uint32_t)y, o, S0 >> o, G.seed)) >> 16;
+    h += (sum * (uint32_t)amp8) >> 3;
+    return min((int)h, G.nz * 3 / 4);
+}
+__device__ inline int band_material(int z, uint32_t r, int type) {            // shape of generate.rs:31-51
+    const int lo = (type == 1) ? 4 : (type == 2) ? 5 : 2;
+    const int mid = (type >= 2) ? 4 : 5;
+    const int hi = 6;
+    if (z < 20) return lo;
+    if (z < 80) return (int)(r % 60u) < z - 20 ? mid : lo;
+    if (z < 160) return (int)(r % 80u) < z - 80 ? hi : mid;
+    return hi;
+}
+
+__global__ void __launch_bounds__(256) k_generate(uint32_t* __restrict__ materials, const __grid_constant__ GenParams G) {
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= G.nx || y >= G.ny) return;
+    int type; const int ht = column_height(G, x, y, &type);
+    // tree of this column's 16x16 cell
+    const uint32_t cx = (uint32_t)x >> 4, cy = (uint32_t)y >> 4;
+    const uint32_t th = hash3(cx, cy, 7u, G.seed);
+    int trunk_lo = 0, trunk_hi = 0, can_lo = 0, can_hi = 0;
+    if ((th & 3u) == 0u) {
+        const int tx = (int)(cx * 16 + 3 + ((th >> 2) & 7u)), ty = (int)(cy * 16 + 3 + ((th >> 5) & 7u));
+        const int tall = 5 + (int)((th >> 8) & 7u);
+        int ttype; const int tb = column_height(G, tx, ty, &ttype);
+        if (x == tx && y == ty) { trunk_lo = tb; trunk_hi = tb + tall; }
+        if (abs(x - tx) <= 2 && abs(y - ty) <= 2) { can_lo = tb + tall; can_hi = tb + tall + 3; }
+    }
+    for (int z = 0; z < G.nz; z++) {
+        uint32_t w = 0;
+        if (z < ht) w = G.words[band_material(z, hash3((uint32_t)x, (uint32_t)y, (uint32_t)z, G.seed ^ 0xA5A5A5A5u), type)];
+        else if (z >= trunk_lo && z < trunk_hi) w = G.words[3];
+        else if (z >= can_lo && z < can_hi) w = G.words[2];
+        materials[((size_t)z * G.ny + y) * G.nx + x] = w;
+    }
+}
+
+}  // namespace
+
+cudaError_t vxrt_launch_build_minefield(uint32_t* materials, uint8_t* minefield, int nx, int ny, int nz,
+                                        const uint32_t* dirty, cudaStream_t s) {
+    const int chunks = (nx >> 6) * (ny >> 6) * (nz >> 6);
+    k_build_minefield<<<chunks, 512, 0, s>>>(materials, minefield, nx, ny, nz, dirty);
+    return cudaGetLastError();
+}
+
+cudaError_t vxrt_launch_apply_edits(uint32_t* materials, uint32_t* dirty, const VxrtEdit* d_edits, size_t n,
+                                    int nx, int ny, int nz, cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    k_apply_edits<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(materials, dirty, d_edits, n, nx, ny, nz);
+    return cudaGetLastError();
+}
+
+cudaError_t vxrt_launch_generate(uint32_t* materials, int nx, int ny, int nz, int kind, uint32_t seed, cudaStream_t s) {
+    GenParams G;
+    G.nx = nx; G.ny = ny; G.nz = nz; G.kind = kind; G.seed = seed;
+    // voxel words of misc/materials.csv through the CSV rule build.rs:50-79 + pack GEN_MATERIALS.rs:44-51
+    const uint32_t words[7] = {0x0u, 0x1FC07Fu, 0x9F73Du, 0xCD319u, 0xCD9B3u, 0xF8D96u, 0x1BBA73u};
+    for (int i = 0; i < 7; i++) G.words[i] = words[i];
+    for (uint32_t k = 0; k < 64; k++) {
+        G.sx[k] = (int)(hash3(k, 0u, 1u, seed) % (uint32_t)nx); G.sy[k] = (int)(hash3(k, 1u, 1u, seed) % (uint32_t)ny);
+        G.stype[k] = (int)(hash3(k, 2u, 1u, seed) % 4u);        G.samp[k] = 4 + (int)(hash3(k, 3u, 1u, seed) % 8u);
+    }
+    dim3 grid((nx + 31) / 32, (ny + 7) / 8);
+    k_generate<<<grid, 256, 0, s>>>(materials, G);
+    return cudaGetLastError();
+}
