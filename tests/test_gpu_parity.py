@@ -1,0 +1,239 @@
+"""GPU parity: libvxrt (through the C ABI) against the CPU oracle on the same seeded inputs.
+Integer outputs (hit voxel, face, material word, step and ray counts, G-buffer codes) are compared
+bit for bit; hit distance within 1e-4; colour within 1/255 (8-bit) or 1/255 of the 16-bit range."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+T_TOL = 1e-4          # north_star: max abs error on hit t
+C8_TOL = 1            # north_star: <= 1/255 per 8-bit channel
+C16_TOL = 257         # the same tolerance on a 16-bit UNORM channel
+
+
+def _frame_block(orc, dims, k=0, n=1, seed=1, lr=(0, 0, 0)):
+    from raytrace_b200 import scenes
+    cam = scenes.camera(dims, k, n)
+    return orc.fill_frame(cam["origin"], cam["heading"], cam["pitch"], cam["sun_angle"], seed, lr)
+
+
+def _compare(orc_frame, R, N, *, denoise, finalize, check_steps=True):
+    B = lambda i: R.read_buffer(i)
+    assert np.array_equal(B(N.BUF_HIT_VOXEL), orc_frame.hit_voxel), "hit voxel"
+    assert np.array_equal(B(N.BUF_HIT_FACE), orc_frame.hit_face), "hit face"
+    assert np.array_equal(B(N.BUF_HIT_WORD), orc_frame.hit_word), "material word"
+    if check_steps:
+        assert np.array_equal(B(N.BUF_STEPS), orc_frame.steps), "march iterations"
+        assert np.array_equal(B(N.BUF_RAYS), orc_frame.rays), "rays per pixel"
+    t_gpu, t_cpu = B(N.BUF_HIT_T), orc_frame.hit_t
+    assert np.array_equal(np.isnan(t_gpu), np.isnan(t_cpu))
+    ok = ~np.isnan(t_cpu)
+    assert np.max(np.abs(t_gpu[ok] - t_cpu[ok]), initial=0.0) <= T_TOL
+    assert np.array_equal(B(N.BUF_DEPTH), orc_frame.depth), "depth"
+    assert np.array_equal(B(N.BUF_NORMAL), orc_frame.normal), "normal"
+    assert np.array_equal(B(N.BUF_ALBEDO), orc_frame.albedo), "albedo"
+    assert np.array_equal(B(N.BUF_EMISSION), orc_frame.emission), "emission"
+    d = lambda a, b: int(np.max(np.abs(a.astype(np.int64) - b.astype(np.int64)), initial=0))
+    assert d(B(N.BUF_FOG), orc_frame.fog) <= C8_TOL, "fog"
+    assert d(B(N.BUF_LIGHTING_RAW), orc_frame.lighting_raw) <= C16_TOL, "lighting (trace)"
+    assert d(B(N.BUF_LIGHTING), orc_frame.lighting) <= C16_TOL, "lighting (after denoise)"
+    if finalize:
+        assert d(B(N.BUF_OUTPUT), orc_frame.output) <= C8_TOL, "output image"
+
+
+@pytest.mark.parametrize("scene,width,height,mode", [
+    ("c1", 256, 256, 0),         # BASELINE config 1: 256x256 primary-ray frame, 128^3 heightmap
+    ("c1", 256, 256, 2),
+    ("small", 72, 40, 2),        # ragged frame (not a multiple of the 8x8 group or the 16x8 block)
+    ("mid", 320, 200, 1),        # reference window size, shadow mode
+    ("mid", 320, 200, 2),
+])
+def test_frame_matches_oracle(orc, world, noise, scene, width, height, mode):
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    dims = scenes.WORLDS[scene][0]
+    m, f = world(scene)
+    blk = _frame_block(orc, dims, seed=7)
+    ref = orc.render(m, f, noise, blk, mode, width, height, denoise=True, finalize=True)
+    with R.Renderer(width, height, dims, mode, N.FLAG_HIT_BUFFERS | N.FLAG_DENOISE | N.FLAG_FINALIZE) as r:
+        r.upload_blue_noise(noise)
+        r.upload_world(m, f)
+        r.set_frame(blk)
+        r.render_frame()
+        _compare(ref, r, N, denoise=True, finalize=True)
+        s = r.frame_stats()
+        assert (s.rays, s.steps, s.hits, s.noise_fetches) == (ref.stats.rays, ref.stats.steps, ref.stats.hits, ref.stats.noise_fetches)
+        assert s.limit_exhausted == ref.stats.ub_limit_exhausted
+
+
+def test_camera_path_and_render_offset(orc, world, noise):
+    """A few frames of the config-2 camera path + a non-zero window centre (toroidal addressing)."""
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    dims = scenes.WORLDS["mid"][0]
+    m, f = world("mid")
+    with R.Renderer(192, 108, dims, N.MODE_FULL, N.FLAG_HIT_BUFFERS | N.FLAG_DENOISE | N.FLAG_FINALIZE) as r:
+        r.upload_blue_noise(noise)
+        r.upload_world(m, f)
+        for k, lr in [(0, (0, 0, 0)), (3, (0, 0, 0)), (7, (16, 0, -16))]:
+            blk = _frame_block(orc, dims, k, 8, seed=100 + k, lr=lr)
+            ref = orc.render(m, f, noise, blk, N.MODE_FULL, 192, 108, denoise=True, finalize=True)
+            r.set_frame(blk)
+            r.render_frame()
+            _compare(ref, r, N, denoise=True, finalize=True)
+
+
+def test_pong_swap_flag(orc, world, noise):
+    """descriptor_sets.rs:37-39: odd denoise passes read swapped depth/normal images."""
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    dims = scenes.WORLDS["c1"][0]
+    m, f = world("c1")
+    blk = _frame_block(orc, dims, seed=3)
+    ref = orc.render(m, f, noise, blk, 2, 160, 96, denoise=True, finalize=True, pong_swap=True)
+    with R.Renderer(160, 96, dims, 2, N.FLAG_HIT_BUFFERS | N.FLAG_DENOISE | N.FLAG_FINALIZE | N.FLAG_PONG_SWAP) as r:
+        r.upload_blue_noise(noise); r.upload_world(m, f); r.set_frame(blk); r.render_frame()
+        _compare(ref, r, N, denoise=True, finalize=True)
+
+
+def test_accumulation(orc, world, noise):
+    """Temporal accumulation (extension): running mean of `light` over seeds 1..6."""
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    dims = scenes.WORLDS["c1"][0]
+    m, f = world("c1")
+    W, H = 128, 96
+    fr = orc.Frame(W, H, accumulate=True)
+    with R.Renderer(W, H, dims, 2, N.FLAG_HIT_BUFFERS | N.FLAG_DENOISE | N.FLAG_FINALIZE | N.FLAG_ACCUMULATE) as r:
+        r.upload_blue_noise(noise); r.upload_world(m, f)
+        for seed in range(1, 7):
+            blk = _frame_block(orc, dims, seed=seed)
+            ref = orc.render(m, f, noise, blk, 2, W, H, denoise=True, finalize=True, frame=fr)
+            r.set_frame(blk); r.render_frame()
+        _compare(ref, r, N, denoise=True, finalize=True)
+        acc = r.read_buffer(N.BUF_ACCUM)
+        assert np.array_equal(acc[..., 3], fr.accum[..., 3])
+        assert np.allclose(acc[..., :3], fr.accum[..., :3], rtol=1e-5, atol=1e-5)
+        r.reset_accumulation()
+        r.render_frame()
+        assert np.all(r.read_buffer(N.BUF_ACCUM)[..., 3] == 1.0)
+
+
+@pytest.mark.parametrize("scene", ["small", "c1", "mid"])
+def test_generator_and_minefield_match_oracle(orc, world, scene):
+    """k_generate == orc_generate_world and k_build_minefield == pack_into (chunk.rs:125-184), bit exact."""
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    dims, kind, seed = scenes.WORLDS[scene]
+    m, f = world(scene)
+    with R.Renderer(64, 64, dims, 0, 0) as r:
+        r.generate_world(kind, seed)
+        gm, gf = r.read_world()
+        assert np.array_equal(gm, m)
+        assert np.array_equal(gf, f)
+        # chunk-wise upload without minefield -> built on the device
+        st = R.ChunkStorage.from_window(m)
+        for (cx, cy, cz), data in st.chunks.items():
+            r.upload_chunk(cx + dims[0] // 128, cy + dims[1] // 128, cz + dims[2] // 128, data.materials, None)
+        gm, gf = r.read_world()
+        assert np.array_equal(gm, m) and np.array_equal(gf, f)
+
+
+def test_pack_into_edge_chunks(orc):
+    """Known-answer chunks of chunk.rs:125-184 through the device builder."""
+    import raytrace_b200 as R
+    solid = 0x1FC07F
+    cases = {"empty": np.zeros((64, 64, 64), np.uint32), "full": np.full((64, 64, 64), solid, np.uint32)}
+    one = np.zeros((64, 64, 64), np.uint32); one[0, 0, 0] = solid; cases["corner"] = one
+    nonsolid = np.full((64, 64, 64), 0x7F, np.uint32); cases["non_solid_words"] = nonsolid   # bit 15 clear -> chunk wiped
+    rng = np.random.default_rng(5)
+    sparse = np.where(rng.random((64, 64, 64)) < 0.001, solid, 0).astype(np.uint32); cases["sparse"] = sparse
+    with R.Renderer(64, 64, (64, 64, 64), 0, 0) as r:
+        for name, words in cases.items():
+            em, ef = orc.pack_chunk(words)
+            r.upload_chunk(0, 0, 0, words, None)
+            gm, gf = r.read_world()
+            assert np.array_equal(gm, em), name
+            assert np.array_equal(gf, ef), name
+
+
+def test_edits_rebuild_matches_oracle(orc, world, noise):
+    """BASELINE config 5 in small: seeded unique edits -> touched chunks rebuilt -> re-render."""
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    dims = scenes.WORLDS["mid"][0]
+    m, f = world("mid")
+    m = m.copy()
+    with R.Renderer(160, 90, dims, 2, N.FLAG_HIT_BUFFERS | N.FLAG_DENOISE | N.FLAG_FINALIZE) as r:
+        r.upload_blue_noise(noise); r.upload_world(m, f)
+        for frame in range(3):
+            e = orc.generate_edits(2000, *dims, 9, frame)
+            assert len(np.unique(e[:, :3], axis=0)) == len(e)
+            orc.apply_edits(m, e)
+            r.apply_edits(e)
+        em, ef = orc.build_minefield(m)
+        gm, gf = r.read_world()
+        assert np.array_equal(gm, em) and np.array_equal(gf, ef)
+        blk = _frame_block(orc, dims, seed=11)
+        ref = orc.render(em, ef, noise, blk, 2, 160, 90, denoise=True, finalize=True)
+        r.set_frame(blk); r.render_frame()
+        _compare(ref, r, N, denoise=True, finalize=True)
+
+
+def test_slice_upload(orc, world):
+    """vxrt_upload_slice == writing a 16-thick slab into the window (terrain_upload.rs:212-267)."""
+    import raytrace_b200 as R
+    from raytrace_b200 import scenes
+    dims = scenes.WORLDS["c1"][0]
+    m, f = world("c1")
+    rng = np.random.default_rng(1)
+    with R.Renderer(64, 64, dims, 0, 0) as r:
+        r.upload_world(m, f)
+        em, ef = m.copy(), f.copy()
+        for axis, off in [(0, 16), (1, 112), (2, 48)]:
+            shape = [dims[2], dims[1], dims[0]]; shape[2 - axis] = 16
+            sm = rng.integers(0, 2 ** 21, size=shape, dtype=np.uint32); sf = rng.integers(0, 7, size=shape, dtype=np.uint8)
+            r.upload_slice(axis, off, sm, sf)
+            sl = [slice(None)] * 3; sl[2 - axis] = slice(off, off + 16)
+            em[tuple(sl)] = sm; ef[tuple(sl)] = sf
+        gm, gf = r.read_world()
+        assert np.array_equal(gm, em) and np.array_equal(gf, ef)
+
+
+def test_row_band_matches_full_frame(orc, world, noise):
+    """Image-space sharding: a handle that renders rows [r0,r1) reproduces those rows of the full frame."""
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    dims = scenes.WORLDS["c1"][0]
+    m, f = world("c1")
+    W, H = 160, 400
+    blk = _frame_block(orc, dims, seed=5)
+    flags = N.FLAG_DENOISE | N.FLAG_FINALIZE
+    with R.Renderer(W, H, dims, 2, flags) as full:
+        full.upload_blue_noise(noise); full.upload_world(m, f); full.set_frame(blk); full.render_frame()
+        img = full.read_output()
+    for r0, r1 in [(0, 136), (136, 264), (264, 400)]:
+        with R.Renderer(W, H, dims, 2, flags, rows=(r0, r1)) as band:
+            band.upload_blue_noise(noise); band.upload_world(m, f); band.set_frame(blk); band.render_frame()
+            out = band.read_output()
+            assert np.array_equal(out[H - r1:H - r0], img[H - r1:H - r0])
+
+
+def test_pipeline_interface(orc, world, noise):
+    """The reference-shaped call sequence: Game -> create_instance -> draw_frame (src/bin/main.rs:8-54)."""
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    dims = scenes.WORLDS["c1"][0]
+    m, f = world("c1")
+    cam = scenes.camera(dims)
+    game = R.Game(args=[*cam["origin"], cam["heading"], cam["pitch"], cam["sun_angle"]], world=R.ChunkStorage.from_window(m, f))
+    pipe = R.create_instance(game, width=128, height=128, window=dims, blue_noise=noise)
+    img1 = pipe.draw_frame(game).copy()
+    assert pipe.seed == 1 and img1.shape == (128, 128, 4) and img1[..., 3].min() == 255
+    blk = np.frombuffer(bytes(pipe.uniform_data), np.uint8)
+    ref = orc.render(m, f, noise, blk, 2, 128, 128, denoise=True, finalize=True)
+    assert np.max(np.abs(img1.astype(int) - ref.output.astype(int))) <= C8_TOL
+    game.borrow_controls_mut().on_pressed("forward"); game.tick(0.1)
+    img2 = pipe.draw_frame(game)
+    assert pipe.seed == 2 and not np.array_equal(img1, img2)
+    pipe.close()
