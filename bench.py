@@ -1,0 +1,308 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the voxel ray-tracing hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl vxrt|reference] [--workload c2|c3|c1|c4]
+
+A "step" is one frame of the workload's camera path: trace -> 6x denoise -> finalize (+ NCCL gather of the
+row bands at N > 1).  Default workload = BASELINE config 2: 1920x1080, primary + 1 shadow ray per pixel,
+512^3 seeded biome world, 64-frame camera path.  One JSON line is printed by rank 0.
+
+  value  : Mrays/s over the whole step, world + frame block already resident in HBM, CUDA-event timed.
+  e2e    : the same through the public call sequence with HOST buffers: vxrt_set_frame(192-byte host block)
+           + vxrt_render_frame + vxrt_read_output(host RGBA8), copies inside the timed region.
+  --impl reference : the reference path's CPU form (the oracle: C++ restatement of the GLSL passes, OpenMP
+           over all host cores; the reference itself has no runnable form here — DESIGN.md §2).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+WORKLOADS = {
+    # name: (scene, width, height, mode, n_path_frames, accumulate, description)
+    "c1": ("c1", 256, 256, 0, 1, False, "256x256 primary-ray frame, 128^3 heightmap world (BASELINE config 1)"),
+    "c2": ("c2", 1920, 1080, 1, 64, False,
+           "1920x1080 primary + 1 shadow ray/pixel, 512^3 biome world, 64-frame camera path (BASELINE config 2)"),
+    "c3": ("c2", 1920, 1080, 2, 1, True,
+           "1080p full lighting (primary + 2 bounces + sky), temporal accumulation, 512^3 biome world (BASELINE config 3)"),
+    "c4": ("c4", 3840, 2160, 2, 16, False, "3840x2160 full lighting on a 2048x2048x256 world (BASELINE config 4)"),
+}
+MODE_NAMES = {0: "primary", 1: "primary+shadow", 2: "full"}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=64)
+    ap.add_argument("--warmup", type=int, default=4)
+    ap.add_argument("--impl", default="vxrt", choices=["vxrt", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the bounded oracle timing on rank 0")
+    ap.add_argument("--no-l2-flush", action="store_true", help="do not flush L2 between timed steps")
+    return ap.parse_args()
+
+
+def frame_blocks(orc, dims, n_path, count):
+    """The 192-byte RaytraceUniformData blocks of the camera path (seed = frame index + 1, pipeline.rs:201)."""
+    from raytrace_b200 import scenes
+    out = []
+    for i in range(count):
+        cam = scenes.camera(dims, i % n_path, n_path)
+        out.append(orc.fill_frame(cam["origin"], cam["heading"], cam["pitch"], cam["sun_angle"], i + 1))
+    return out
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(device), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            pass
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            out, _ = self.p.communicate(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+            out, _ = self.p.communicate()
+        sm, mx, reasons = [], [], set()
+        for ln in out.splitlines():
+            t = [x.strip() for x in ln.split(",")]
+            if len(t) < 9:
+                continue
+            try:
+                sm.append(float(t[1])); mx.append(float(t[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), t[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def bands_for(height, n):
+    """Contiguous row bands, multiples of 8 rows (the 8x8 shader group, constants.rs:33)."""
+    edges = [min(height, (height * i // n + 7) // 8 * 8) for i in range(n)] + [height]
+    return [(edges[i], edges[i + 1]) for i in range(n)]
+
+
+def algo_bytes_trace(stats, pixels):
+    """per ray (1 + S_r) minefield bytes + 4 B if it ends in a hit; per pixel 23 B of G-buffer
+    stores; 4 B per blue-noise fetch."""
+    return (stats.rays + stats.steps) + 4 * stats.hits + 23 * pixels + 4 * stats.noise_fetches
+
+
+def time_oracle(orc, world, noise, blocks, mode, W, H, steps, warmup, accumulate):
+    m, f = world
+    fr = orc.Frame(W, H, accumulate=accumulate)
+    times, rays = [], 0
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        orc.render(m, f, noise, blocks[i % len(blocks)], mode, W, H, denoise=True, finalize=True, frame=fr)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt); rays += fr.stats.rays
+    return sum(times), rays
+
+
+def run_reference(args, rank, world_size):
+    """--impl reference: the reference path's CPU form (oracle) on the host cores, rank 0 only."""
+    if rank != 0:
+        return
+    from oracle import orc
+    from raytrace_b200 import scenes
+    scene, W, H, mode, n_path, accumulate, desc = WORKLOADS[args.workload]
+    dims, kind, seed = scenes.WORLDS[scene]
+    m = orc.generate_world(*dims, kind, seed)
+    world = orc.build_minefield(m)
+    noise = orc.blue_noise()
+    blocks = frame_blocks(orc, dims, n_path, args.warmup + args.steps)
+    total, rays = time_oracle(orc, world, noise, blocks, mode, W, H, args.steps, args.warmup, accumulate)
+    cores = os.cpu_count()
+    v = rays / total / 1e6
+    line = {"metric": "Mrays/s", "value": v, "unit": "Mrays/s", "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3, "frames_per_s": args.steps / total,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": desc, "mode": MODE_NAMES[mode], "width": W, "height": H, "world": list(dims)},
+            "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": cores, "kind": "port",
+                             "sample": f"{args.steps} full frames (trace + 6 denoise + finalize) of the workload"},
+            "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "reference GLSL/Vulkan path cannot run on this box; this is the CPU restatement (oracle/) with OpenMP"}
+    print(json.dumps(line), flush=True)
+
+
+def run_vxrt(args, rank, world_size, local_rank):
+    import ctypes as C
+    import torch
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; libvxrt has no CPU path (use --impl reference for the CPU baseline)")
+    dist = None
+    if world_size > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    scene, W, H, mode, n_path, accumulate, desc = WORKLOADS[args.workload]
+    dims, kind, seed = scenes.WORLDS[scene]
+    band = bands_for(H, world_size)[rank]
+    flags = N.FLAG_DENOISE | N.FLAG_FINALIZE | (N.FLAG_ACCUMULATE if accumulate else 0)
+    r = R.Renderer(W, H, dims, mode, flags, device=local_rank, rows=band if world_size > 1 else None)
+    noise = R.world.default_blue_noise()
+    r.upload_blue_noise(noise)
+    r.generate_world(kind, seed)                 # world replicated: every rank generates the same seeded world
+    lib, h = N.lib, r.handle
+    if world_size > 1:
+        ident = [None]
+        if rank == 0:
+            buf = (C.c_uint8 * N.COMM_ID_BYTES)()
+            assert lib.vxrt_comm_unique_id(buf, N.COMM_ID_BYTES) == 0
+            ident[0] = bytes(buf)
+        dist.broadcast_object_list(ident, src=0)
+        r._check(lib.vxrt_comm_init(h, ident[0], N.COMM_ID_BYTES, rank, world_size))
+
+    # frame blocks: host-side parameter fill (pipeline.rs:191-207); the oracle module is only the source of
+    # the seeded camera blocks here, exactly as tests/ use it
+    from oracle import orc
+    n_frames = args.warmup + args.steps
+    blocks = frame_blocks(orc, dims, n_path, n_frames)
+    stream = torch.cuda.ExternalStream(r.cuda_stream(), device=torch.device("cuda", local_rank))
+    flush = None if args.no_l2_flush else torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local_rank}")
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(i):
+        r.set_frame(blocks[i])
+        r.render_frame()
+        if world_size > 1:
+            r._check(lib.vxrt_comm_gather_output(h, 0))
+
+    # ---- device-resident timing: per-step CUDA events on the handle's stream, L2 flushed between steps ----
+    for i in range(args.warmup):
+        step(i); r.sync()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    tot = dict(rays=0, steps=0, hits=0, noise=0, limit=0, trace_ms=0.0, denoise_ms=0.0, finalize_ms=0.0, algo=0)
+    barrier()
+    clocks = ClockSampler(local_rank)
+    wall0 = time.perf_counter()
+    for k in range(args.steps):
+        if flush is not None:
+            with torch.cuda.stream(stream):
+                flush.fill_(k & 0xFF)            # evicts L2 (126 MB) — untimed, before the step's start event
+        ev[k][0].record(stream)
+        step(args.warmup + k)
+        ev[k][1].record(stream)
+        s = r.frame_stats()                      # syncs the stream; per-kernel event times of this step
+        tot["rays"] += s.rays; tot["steps"] += s.steps; tot["hits"] += s.hits; tot["noise"] += s.noise_fetches
+        tot["limit"] += s.limit_exhausted
+        tot["trace_ms"] += s.trace_ms; tot["denoise_ms"] += s.denoise_ms; tot["finalize_ms"] += s.finalize_ms
+        traced_rows = min(H, band[1] + 117) - max(0, band[0] - 117) if world_size > 1 else H
+        tot["algo"] += algo_bytes_trace(s, traced_rows * W)
+    barrier()
+    wall = time.perf_counter() - wall0
+    clk = clocks.stop()
+    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+
+    # ---- end to end through the public call sequence with host buffers -------------------------------------
+    out_host = np.empty((H, W, 4), np.uint8)
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        step(args.warmup + k)
+        if rank == 0:
+            r.read_output(out_host)              # D2H of the gathered frame (sync)
+        else:
+            r.sync()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+
+    # ---- reduce over ranks: time = max, work = sum ---------------------------------------------------------
+    vals = torch.tensor([dev_ms, e2e_s, wall], dtype=torch.float64, device=f"cuda:{local_rank}")
+    sums = torch.tensor([tot["rays"], tot["steps"], tot["hits"], tot["algo"], tot["limit"]], dtype=torch.float64,
+                        device=f"cuda:{local_rank}")
+    if dist is not None:
+        dist.all_reduce(vals, op=dist.ReduceOp.MAX)
+        dist.all_reduce(sums, op=dist.ReduceOp.SUM)
+    dev_ms, e2e_s, wall = vals.tolist()
+    rays, steps_total, hits, algo, limit = sums.tolist()
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        trace_s = tot["trace_ms"] / 1e3
+        achieved = algo_bytes_rank0 = tot["algo"] / trace_s / 1e9
+        line = {
+            "metric": "Mrays/s", "value": rays / (dev_ms / 1e3) / 1e6, "unit": "Mrays/s", "n_gpus": world_size,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps,
+            "frames_per_s": args.steps / (dev_ms / 1e3), "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": desc, "mode": MODE_NAMES[mode], "width": W, "height": H, "world": list(dims),
+                       "passes": "trace + 6 denoise + finalize" + (" + NCCL band gather" if world_size > 1 else ""),
+                       "parallelism": f"image row bands x{world_size}, world replicated",
+                       "l2": "inputs 640 MiB > L2, not flushed" if flush is None else "flushed between steps (256 MiB fill, untimed)"},
+            "rays_per_frame": rays / args.steps, "mean_steps_per_ray": steps_total / max(rays, 1.0),
+            "limit_exhausted": limit,
+            "kernel_ms_per_step_rank0": {"trace": tot["trace_ms"] / args.steps, "denoise": tot["denoise_ms"] / args.steps,
+                                          "finalize": tot["finalize_ms"] / args.steps},
+            "trace_mrays_per_s_rank0": tot["rays"] / trace_s / 1e6,
+            "e2e": {"value": rays / e2e_s / 1e6, "unit": "Mrays/s", "frames_per_s": args.steps / e2e_s,
+                    "h2d_bytes_per_step": 192, "d2h_bytes_per_step": W * H * 4},
+            "gpu_launches": args.steps * 8 * world_size,
+            "roofline": {"kernel": "k_trace", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
+                         "algo_bytes_per_launch": tot["algo"] / args.steps, "launch_ms": tot["trace_ms"] / args.steps,
+                         "traffic": None},
+            "clocks": clk, "wall_s_timed_loop": wall,
+        }
+        if not args.no_cpu_baseline and world_size == 1:
+            m, f = r.read_world()
+            nb = 2
+            t, cr = time_oracle(orc, (m, f), noise, blocks[args.warmup:], mode, W, H, nb, 1, accumulate)
+            line["cpu_baseline"] = {"value": cr / t / 1e6, "unit": "Mrays/s", "frames_per_s": nb / t, "cores": os.cpu_count(),
+                                    "kind": "port", "sample": f"{nb} full frames of the same workload through the oracle (OpenMP)"}
+        print(json.dumps(line), flush=True)
+    r.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world_size = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world_size)
+    else:
+        run_vxrt(args, rank, world_size, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -27,7 +27,8 @@ typedef enum VxrtStatus {
     VXRT_ERR_INVALID = -1,   /* bad argument / configuration             */
     VXRT_ERR_CUDA = -2,      /* CUDA runtime error (text in last_error)   */
     VXRT_ERR_STATE = -3,     /* call made in the wrong order              */
-    VXRT_ERR_SIZE = -4       /* host buffer too small                     */
+    VXRT_ERR_SIZE = -4,      /* host buffer too small                     */
+    VXRT_ERR_COMM = -5       /* NCCL unavailable or an NCCL call failed   */
 } VxrtStatus;
 
 /* Truncations of raytrace.comp:main (:320-350).  Only FULL is reference behaviour. */
@@ -159,6 +160,19 @@ size_t vxrt_buffer_bytes(const VxrtHandle* h, int buffer_id);
 void* vxrt_device_buffer(VxrtHandle* h, int buffer_id);     /* zero-copy consumers (NCCL gather) */
 void* vxrt_cuda_stream(VxrtHandle* h);                      /* cudaStream_t of the handle         */
 int  vxrt_frame_stats(VxrtHandle* h, VxrtFrameStats* out);  /* syncs the stream                   */
+
+/* ---- multi-GPU (no reference equivalent: the reference drives one Vulkan queue, pipeline.rs:229-235) --
+ * One handle per GPU/process; the world is replicated and each handle renders the row band given
+ * at vxrt_create.  NCCL (bound at run time) moves only the final image bands and edit lists. */
+#define VXRT_COMM_ID_BYTES 128
+/* On one rank: an NCCL unique id to hand to every rank by any host channel. */
+int  vxrt_comm_unique_id(void* id_out, size_t nbytes);
+int  vxrt_comm_init(VxrtHandle* h, const void* id, size_t nbytes, int rank, int nranks);
+/* After vxrt_render_frame: every rank's RGBA8 band lands in root's VXRT_BUF_OUTPUT (root < 0: in
+ * every rank's).  Asynchronous on the handle's stream. */
+int  vxrt_comm_gather_output(VxrtHandle* h, int root);
+/* Broadcast root's host edit list (n given on every rank) and apply it on every replica. */
+int  vxrt_comm_broadcast_edits(VxrtHandle* h, const VxrtEdit* edits, size_t n, int root);
 
 #ifdef __cplusplus
 }

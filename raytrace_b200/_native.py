@@ -1,7 +1,7 @@
 """ctypes binding of libvxrt.so — the C ABI declared in include/vxrt.h.
 
 The library is the product: if it is missing this module raises at import (there is no CPU or
-PyTorch fallback anywhere in the package).  Build it with ``python -m raytrace_b200.build`` or
+PyTorch fallback anywhere in the package).  Build it with ``python raytrace_b200/build.py`` or
 ``__graft_entry__.build()``.
 """
 import ctypes as C
@@ -85,14 +85,19 @@ SYMBOLS = {
     "vxrt_device_buffer": (C.c_void_p, [_H, C.c_int]),
     "vxrt_cuda_stream": (C.c_void_p, [_H]),
     "vxrt_frame_stats": (C.c_int, [_H, C.POINTER(VxrtFrameStats)]),
+    "vxrt_comm_unique_id": (C.c_int, [C.c_void_p, C.c_size_t]),
+    "vxrt_comm_init": (C.c_int, [_H, C.c_void_p, C.c_size_t, C.c_int, C.c_int]),
+    "vxrt_comm_gather_output": (C.c_int, [_H, C.c_int]),
+    "vxrt_comm_broadcast_edits": (C.c_int, [_H, C.c_void_p, C.c_size_t, C.c_int]),
 }
+COMM_ID_BYTES = 128
 
 
 def load():
     if not os.path.exists(LIB_PATH):
         raise ImportError(
             f"{LIB_PATH} is missing: libvxrt (the CUDA implementation) has not been built and there is no "
-            "fallback path.  Run `python -m raytrace_b200.build`.")
+            "fallback path.  Run `python raytrace_b200/build.py`.")
     lib = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
     for name, (res, args) in SYMBOLS.items():
         fn = getattr(lib, name)          # AttributeError here = header and library disagree

@@ -1,6 +1,6 @@
 """Builds raytrace_b200/libvxrt.so (hand-written CUDA for sm_100a) with nvcc, in-tree.
 
-    python -m raytrace_b200.build [--force] [--verbose]
+    python raytrace_b200/build.py [--force] [--verbose]
 
 nvcc cross-compiles without a GPU.  -lineinfo keeps ncu's source page mapped to the .cu files; the
 host side is compiled with -ffp-contract=off because the per-frame constants computed on the host

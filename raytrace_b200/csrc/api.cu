@@ -188,6 +188,7 @@ int vxrt_create(const VxrtConfig* cfg, VxrtHandle** out) {
     h->d_rays = nullptr; h->d_accum = nullptr; h->d_counters = nullptr;
     h->have_frame = h->have_world = h->have_noise = h->rendered = false;
     h->frames_accumulated = 0;
+    h->comm = nullptr; h->rank = 0; h->nranks = 1;
     memset(&h->frame, 0, sizeof h->frame);
     h->h_noise.assign((size_t)VXRT_NOISE_SIZE * VXRT_NOISE_SIZE * 4, 0);
 
@@ -237,6 +238,7 @@ void vxrt_destroy(VxrtHandle* h) {
     if (!h) return;
     cudaSetDevice(h->cfg.device);
     if (h->stream) cudaStreamSynchronize(h->stream);
+    vxrt_comm_release(h);
     void* ptrs[] = {h->d_materials, h->d_minefield, h->d_noise, h->d_lut, h->d_dirty, h->d_edits, h->d_lighting, h->d_pong,
                     h->d_lighting_raw, h->d_depth, h->d_normal, h->d_albedo, h->d_emission, h->d_fog, h->d_output,
                     h->d_hit_voxel, h->d_hit_face, h->d_hit_word, h->d_hit_t, h->d_steps, h->d_rays, h->d_accum, h->d_counters};

@@ -56,7 +56,10 @@ struct VxrtHandle {
     unsigned long long* d_counters;
     VxrtFrameParams frame; bool have_frame, have_world, have_noise, rendered;
     uint32_t frames_accumulated;
+    // multi-GPU (comm.cu)
+    void* comm; int rank, nranks; std::vector<int32_t> bands;   // bands[2r], bands[2r+1] = rows of rank r
 };
+void vxrt_comm_release(VxrtHandle* h);
 
 // launchers (each returns the cudaGetLastError() of its launch)
 cudaError_t vxrt_launch_trace(const TraceParams& p, cudaStream_t s);
