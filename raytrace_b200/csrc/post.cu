@@ -12,53 +12,104 @@ __device__ __forceinline__ uint32_t unorm_store(float x, float maxv) {
     return __float2uint_rn(fmul(fminf(fmaxf(x, 0.0f), 1.0f), maxv));
 }
 
-// bilateral_denoise.comp:40-86, source order
-__constant__ int8_t c_tap_dx[36] = {0, 0, 1, -1, 1, -1, -1, 1, 2, -2, 0, 0, 2, -2, -2, 2, 2, -2, -2, 2, 1, -1, -1, 1,
-                                    3, -3, 0, 0, 3, -3, -3, 3, 1, -1, -1, 1};
-__constant__ int8_t c_tap_dy[36] = {1, -1, 0, 0, 1, 1, -1, -1, 0, 0, 2, -2, 2, 2, -2, -2, 1, 1, -1, -1, 2, 2, -2, -2,
-                                    0, 0, 3, -3, 1, 1, -1, -1, 3, 3, -3, -3};
-__constant__ float c_tap_w[36] = {0.092566f, 0.092566f, 0.092566f, 0.092566f, 0.058434f, 0.058434f, 0.058434f, 0.058434f,
-                                  0.023205f, 0.023205f, 0.023205f, 0.023205f, 0.003672f, 0.003672f, 0.003672f, 0.003672f,
-                                  0.014648f, 0.014648f, 0.014648f, 0.014648f, 0.014648f, 0.014648f, 0.014648f, 0.014648f,
-                                  0.002289f, 0.002289f, 0.002289f, 0.002289f, 0.001445f, 0.001445f, 0.001445f, 0.001445f,
-                                  0.001445f, 0.001445f, 0.001445f, 0.001445f};
+// bilateral_denoise.comp:35-89 as a shared-memory tiled kernel.  SWAP reproduces the pong descriptor set
+// (descriptor_sets.rs:37-39: odd passes read the R8 normal image as "depth" and the R16 depth image as
+// "normal").
+//
+// The filter is colour work: its contract is the stated tolerance (<= 1/255 per 8-bit channel after
+// finalize), not bit equality, so this kernel uses FMA contraction, a reciprocal-multiply for the UNORM
+// decode and MUFU.RCP for the 36 weight divisions.  The 16-bit quantisation point after every pass is kept.
+//
+// Tiling: a pass with dilation S only couples pixels whose y differ by multiples of S, so
+// a CTA owns 128 contiguous x (coalesced rows) x TH rows of ONE y-residue class and stages
+// (128 + 6S) x (TH + 6) texels in shared memory, decoded once to {r,g,b,dist} floats + the normal code.
+// Every tap is then one LDS.128 + one LDS.U16 at a compile-time offset; consecutive lanes read consecutive
+// texels (no bank conflicts beyond the 4 wavefronts a 512-byte row needs).
+constexpr int DN_TX = 128;                     // pixels per CTA row (= threads in x)
+template <int S, int TH> struct DnTile {
+    static constexpr int W = DN_TX + 6 * S, R = TH + 6, N = W * R;
+    static constexpr size_t BYTES = (size_t)N * (sizeof(float4) + sizeof(uint16_t));
+};
 
-// bilateral_denoise.comp:35-89.  SWAP reproduces the pong descriptor set (descriptor_sets.rs:37-39).
-template <bool SWAP>
+template <int S, int TH, bool SWAP>
 __global__ void __launch_bounds__(256) k_denoise(const ushort4* __restrict__ src, ushort4* __restrict__ dst,
                                                  const uint16_t* __restrict__ depth, const uint8_t* __restrict__ normal,
-                                                 int width, int height, int size, int row0, int row1) {
-    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = row0 + blockIdx.y * 8 + (threadIdx.x >> 5);
-    if (x >= width || y >= row1) return;
-    const size_t pi = (size_t)y * width + x;
-    const uint32_t dv = SWAP ? (uint32_t)normal[pi] : (uint32_t)depth[pi];
-    const uint32_t center_normal = SWAP ? (uint32_t)depth[pi] : (uint32_t)normal[pi];
-    const ushort4 c = src[pi];
-    if (center_normal >= 16) { dst[pi] = c; return; }                          // :88-89
-    const float center_distance = fdiv((float)dv, 256.0f);                     // :37
-    float total_weight = 0.146634f;                                            // :41
-    float sr = fmul(fdiv((float)c.x, 65535.0f), total_weight), sg = fmul(fdiv((float)c.y, 65535.0f), total_weight),
-          sb = fmul(fdiv((float)c.z, 65535.0f), total_weight);
-#pragma unroll 4
-    for (int t = 0; t < 36; t++) {                                             // SAMPLE, :23-33
-        int qx = x + c_tap_dx[t] * size, qy = y + c_tap_dy[t] * size;
-        qx = min(max(qx, 0), width - 1); qy = min(max(qy, 0), height - 1);     // sampleAt, :14-21
-        const size_t qi = (size_t)qy * width + qx;
-        const uint32_t qd = SWAP ? (uint32_t)normal[qi] : (uint32_t)depth[qi];
-        const uint32_t qn = SWAP ? (uint32_t)depth[qi] : (uint32_t)normal[qi];
-        const float dist = fdiv((float)qd, 256.0f);
-        const float dd = fmul(4.0f, fabsf(fsub(center_distance, dist)));
-        const float nd = qn == center_normal ? 0.0f : 10.0f;
-        const float weight = fdiv(c_tap_w[t], fadd(fadd(dd, nd), 1.0f));
-        total_weight = fadd(total_weight, weight);
-        const ushort4 q = src[qi];
-        sr = fadd(sr, fmul(fdiv((float)q.x, 65535.0f), weight));
-        sg = fadd(sg, fmul(fdiv((float)q.y, 65535.0f), weight));
-        sb = fadd(sb, fmul(fdiv((float)q.z, 65535.0f), weight));
+                                                 int width, int height, int row0, int row1, int groups) {
+    using T = DnTile<S, TH>;
+    extern __shared__ float4 dn_tile[];
+    uint16_t* dn_nrm = reinterpret_cast<uint16_t*>(dn_tile + T::N);
+    const int tid = threadIdx.y * DN_TX + threadIdx.x;
+    const int bx = blockIdx.x * DN_TX;
+    const int res = blockIdx.y / groups, grp = blockIdx.y - res * groups;   // y-residue class, group of TH decimated rows
+    const int ybase = row0 + res + grp * TH * S;                             // G-buffer row of decimated row 0
+    // stage: texel (tx, ty) <- image (clamp(bx + tx - 3S), clamp(ybase + (ty - 3) * S))   (sampleAt, :14-21)
+    for (int e = tid; e < T::N; e += 256) {
+        const int ty = e / T::W, tx = e - ty * T::W;
+        const int gx = min(max(bx + tx - 3 * S, 0), width - 1), gy = min(max(ybase + (ty - 3) * S, 0), height - 1);
+        const size_t gi = (size_t)gy * width + gx;
+        const ushort4 q = __ldg(src + gi);
+        const uint32_t d = __ldg(depth + gi), n = __ldg(normal + gi);
+        const float k = 1.0f / 65535.0f;
+        dn_tile[e] = make_float4((float)q.x * k, (float)q.y * k, (float)q.z * k, (float)(SWAP ? n : d) * (1.0f / 256.0f));   // :37
+        dn_nrm[e] = (uint16_t)(SWAP ? d : n);
     }
-    dst[pi] = make_ushort4((unsigned short)unorm_store(fdiv(sr, total_weight), 65535.0f),
-                           (unsigned short)unorm_store(fdiv(sg, total_weight), 65535.0f),
-                           (unsigned short)unorm_store(fdiv(sb, total_weight), 65535.0f), 65535);   // :87
+    __syncthreads();
+    const int x = bx + threadIdx.x;
+    if (x >= width) return;
+#pragma unroll 1
+    for (int j = threadIdx.y; j < TH; j += 2) {
+        const int y = ybase + j * S;
+        if (y >= row1) break;
+        const int c = (j + 3) * T::W + threadIdx.x + 3 * S;
+        const size_t pi = (size_t)y * width + x;
+        const uint32_t cn = dn_nrm[c];
+        if (cn >= 16) { dst[pi] = __ldg(src + pi); continue; }                 // :88-89
+        const float4 cv = dn_tile[c];
+        float tw = 0.146634f;                                                  // :41
+        float sr = cv.x * tw, sg = cv.y * tw, sb = cv.z * tw;
+#define DN_TAP(DX, DY, WGT)                                                                       \
+        {                                                                                         \
+            const int o = c + (DY) * T::W + (DX) * S;                                             \
+            const float4 q = dn_tile[o];                                                          \
+            const float den = fmaf(4.0f, fabsf(cv.w - q.w), dn_nrm[o] == cn ? 1.0f : 11.0f);      \
+            const float w = (WGT) * __frcp_rn(den);                                               \
+            tw += w; sr = fmaf(q.x, w, sr); sg = fmaf(q.y, w, sg); sb = fmaf(q.z, w, sb);         \
+        }
+        // SAMPLE list, bilateral_denoise.comp:43-86, source order
+        DN_TAP(0, 1, 0.092566f) DN_TAP(0, -1, 0.092566f) DN_TAP(1, 0, 0.092566f) DN_TAP(-1, 0, 0.092566f)
+        DN_TAP(1, 1, 0.058434f) DN_TAP(-1, 1, 0.058434f) DN_TAP(-1, -1, 0.058434f) DN_TAP(1, -1, 0.058434f)
+        DN_TAP(2, 0, 0.023205f) DN_TAP(-2, 0, 0.023205f) DN_TAP(0, 2, 0.023205f) DN_TAP(0, -2, 0.023205f)
+        DN_TAP(2, 2, 0.003672f) DN_TAP(-2, 2, 0.003672f) DN_TAP(-2, -2, 0.003672f) DN_TAP(2, -2, 0.003672f)
+        DN_TAP(2, 1, 0.014648f) DN_TAP(-2, 1, 0.014648f) DN_TAP(-2, -1, 0.014648f) DN_TAP(2, -1, 0.014648f)
+        DN_TAP(1, 2, 0.014648f) DN_TAP(-1, 2, 0.014648f) DN_TAP(-1, -2, 0.014648f) DN_TAP(1, -2, 0.014648f)
+        DN_TAP(3, 0, 0.002289f) DN_TAP(-3, 0, 0.002289f) DN_TAP(0, 3, 0.002289f) DN_TAP(0, -3, 0.002289f)
+        DN_TAP(3, 1, 0.001445f) DN_TAP(-3, 1, 0.001445f) DN_TAP(-3, -1, 0.001445f) DN_TAP(3, -1, 0.001445f)
+        DN_TAP(1, 3, 0.001445f) DN_TAP(-1, 3, 0.001445f) DN_TAP(-1, -3, 0.001445f) DN_TAP(1, -3, 0.001445f)
+#undef DN_TAP
+        const float inv = __frcp_rn(tw);
+        dst[pi] = make_ushort4((unsigned short)unorm_store(sr * inv, 65535.0f), (unsigned short)unorm_store(sg * inv, 65535.0f),
+                               (unsigned short)unorm_store(sb * inv, 65535.0f), 65535);   // :87
+    }
+}
+
+template <int S, int TH>
+cudaError_t launch_denoise_s(const ushort4* src, ushort4* dst, const uint16_t* depth, const uint8_t* normal, int width,
+                             int height, int swap, int row0, int row1, cudaStream_t s) {
+    using T = DnTile<S, TH>;
+    const int rows = row1 - row0;
+    const int per_res = (rows + S - 1) / S;                 // decimated rows of the fullest residue class
+    const int groups = (per_res + TH - 1) / TH;
+    dim3 grid((width + DN_TX - 1) / DN_TX, S * groups), block(DN_TX, 2);
+    static bool attr_set = false;                           // per template instantiation
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(k_denoise<S, TH, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T::BYTES);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_denoise<S, TH, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T::BYTES);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    if (swap) k_denoise<S, TH, true><<<grid, block, T::BYTES, s>>>(src, dst, depth, normal, width, height, row0, row1, groups);
+    else k_denoise<S, TH, false><<<grid, block, T::BYTES, s>>>(src, dst, depth, normal, width, height, row0, row1, groups);
+    return cudaGetLastError();
 }
 
 // finalize.comp:21-31
@@ -106,10 +157,14 @@ __global__ void __launch_bounds__(256) k_finalize(const uchar4* __restrict__ alb
 cudaError_t vxrt_launch_denoise(const ushort4* src, ushort4* dst, const uint16_t* depth, const uint8_t* normal,
                                 int width, int height, int size, int swap, int row0, int row1, cudaStream_t s) {
     if (row1 <= row0) return cudaSuccess;
-    dim3 grid((width + 31) / 32, (row1 - row0 + 7) / 8);
-    if (swap) k_denoise<true><<<grid, 256, 0, s>>>(src, dst, depth, normal, width, height, size, row0, row1);
-    else k_denoise<false><<<grid, 256, 0, s>>>(src, dst, depth, normal, width, height, size, row0, row1);
-    return cudaGetLastError();
+    switch (size) {                                        // pipeline.rs:103: sizes 1, 2, 4, 8, 8, 16
+        case 1: return launch_denoise_s<1, 16>(src, dst, depth, normal, width, height, swap, row0, row1, s);
+        case 2: return launch_denoise_s<2, 16>(src, dst, depth, normal, width, height, swap, row0, row1, s);
+        case 4: return launch_denoise_s<4, 16>(src, dst, depth, normal, width, height, swap, row0, row1, s);
+        case 8: return launch_denoise_s<8, 8>(src, dst, depth, normal, width, height, swap, row0, row1, s);
+        case 16: return launch_denoise_s<16, 8>(src, dst, depth, normal, width, height, swap, row0, row1, s);
+        default: return cudaErrorInvalidValue;
+    }
 }
 
 cudaError_t vxrt_launch_finalize(const uchar4* albedo, const uchar4* emission, const uchar4* fog, const ushort4* lighting,
