@@ -62,47 +62,57 @@ def frame_blocks(orc, dims, n_path, count):
 
 
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock + throttle reasons sampled DURING the timed region (the B200_PROFILING.md clocks line, read
+    through NVML in a thread every 2 ms because the timed loop is only tens of milliseconds long)."""
 
     def __init__(self, device):
-        self.p = None
+        import threading
+        self.samples, self.max_mhz, self.reasons, self._stop = [], None, set(), threading.Event()
+        self.err = None
         try:
-            self.p = subprocess.Popen(["nvidia-smi", "-i", str(device), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                       "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-        except OSError:
-            pass
+            import pynvml
+            pynvml.nvmlInit()
+            # NVML indexes physical GPUs; honour CUDA_VISIBLE_DEVICES when it lists ordinals
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = device
+            if vis:
+                ids = [v.strip() for v in vis.split(",") if v.strip()]
+                if device < len(ids) and ids[device].isdigit():
+                    idx = int(ids[device])
+            self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception as e:  # noqa: BLE001
+            self.err = f"nvml unavailable: {e}"
+            return
+        self.t = threading.Thread(target=self._run, daemon=True)
+        self.t.start()
+
+    def _run(self):
+        nv = self.nv
+        names = {"hw_slowdown": nv.nvmlClocksEventReasonHwSlowdown if hasattr(nv, "nvmlClocksEventReasonHwSlowdown") else 0x8,
+                 "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:  # noqa: BLE001
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception as e:  # noqa: BLE001
+                self.err = str(e)
+                break
+            self._stop.wait(0.002)
 
     def stop(self):
-        if self.p is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.p.terminate()
-        try:
-            out, _ = self.p.communicate(timeout=5)
-        except subprocess.TimeoutExpired:
-            self.p.kill()
-            out, _ = self.p.communicate()
-        sm, mx, reasons = [], [], set()
-        for ln in out.splitlines():
-            t = [x.strip() for x in ln.split(",")]
-            if len(t) < 9:
-                continue
-            try:
-                sm.append(float(t[1])); mx.append(float(t[2]))
-            except ValueError:
-                continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), t[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
-
-
-def bands_for(height, n):
-    """Contiguous row bands, multiples of 8 rows (the 8x8 shader group, constants.rs:33)."""
-    edges = [min(height, (height * i // n + 7) // 8 * 8) for i in range(n)] + [height]
-    return [(edges[i], edges[i + 1]) for i in range(n)]
+        if self.err and not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "samples": 0, "reasons": [self.err]}
+        self._stop.set()
+        self.t.join(timeout=2)
+        return {"sm_mhz": statistics.median(self.samples) if self.samples else None, "sm_max_mhz": self.max_mhz,
+                "samples": len(self.samples), "reasons": sorted(self.reasons)}
 
 
 def algo_bytes_trace(stats, pixels):
@@ -165,7 +175,7 @@ def run_vxrt(args, rank, world_size, local_rank):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     scene, W, H, mode, n_path, accumulate, desc = WORKLOADS[args.workload]
     dims, kind, seed = scenes.WORLDS[scene]
-    band = bands_for(H, world_size)[rank]
+    band = R.plan_bands(H, world_size)[rank]
     flags = N.FLAG_DENOISE | N.FLAG_FINALIZE | (N.FLAG_ACCUMULATE if accumulate else 0)
     r = R.Renderer(W, H, dims, mode, flags, device=local_rank, rows=band if world_size > 1 else None)
     noise = R.world.default_blue_noise()
@@ -220,8 +230,7 @@ def run_vxrt(args, rank, world_size, local_rank):
         tot["rays"] += s.rays; tot["steps"] += s.steps; tot["hits"] += s.hits; tot["noise"] += s.noise_fetches
         tot["limit"] += s.limit_exhausted
         tot["trace_ms"] += s.trace_ms; tot["denoise_ms"] += s.denoise_ms; tot["finalize_ms"] += s.finalize_ms
-        traced_rows = min(H, band[1] + 117) - max(0, band[0] - 117) if world_size > 1 else H
-        tot["algo"] += algo_bytes_trace(s, traced_rows * W)
+        tot["algo"] += algo_bytes_trace(s, (band[1] - band[0]) * W)   # own rows only (halo rows are extra, uncounted work)
     barrier()
     wall = time.perf_counter() - wall0
     clk = clocks.stop()

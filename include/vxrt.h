@@ -98,7 +98,8 @@ typedef enum VxrtBufferId {
     VXRT_BUF_COUNT_
 } VxrtBufferId;
 
-/* Counters of the last rendered frame (whole rows this handle rendered). */
+/* Counters of the last rendered frame over the handle's own rows [row_begin,row_end); rays traced for
+ * the denoise halo of a band are not counted. */
 typedef struct VxrtFrameStats {
     uint64_t rays, steps, hits, noise_fetches;
     uint64_t limit_exhausted;    /* rays that ran out of max_steps (reference UB) */
@@ -160,6 +161,15 @@ size_t vxrt_buffer_bytes(const VxrtHandle* h, int buffer_id);
 void* vxrt_device_buffer(VxrtHandle* h, int buffer_id);     /* zero-copy consumers (NCCL gather) */
 void* vxrt_cuda_stream(VxrtHandle* h);                      /* cudaStream_t of the handle         */
 int  vxrt_frame_stats(VxrtHandle* h, VxrtFrameStats* out);  /* syncs the stream                   */
+
+/* ---- image-space sharding plan: pure host arithmetic, usable without a device ------------------------ */
+/* rows[2r], rows[2r+1] = band [begin,end) of rank r: contiguous, edges on multiples of 8 rows
+ * (the 8x8 shader group, constants.rs:33). */
+int  vxrt_plan_bands(int height, int nranks, int32_t* rows /* 2*nranks */);
+/* For a handle rendering [row_begin,row_end): rows[0..1] = rows the trace pass must cover (band + 117-row
+ * denoise halo, clipped), rows[2+2k..3+2k] = rows denoise pass k (sizes 1,2,4,8,8,16, pipeline.rs:103)
+ * must cover so that the final band only ever read valid rows. */
+int  vxrt_plan_passes(int height, int row_begin, int row_end, uint32_t flags, int32_t* rows /* 14 */);
 
 /* ---- multi-GPU (no reference equivalent: the reference drives one Vulkan queue, pipeline.rs:229-235) --
  * One handle per GPU/process; the world is replicated and each handle renders the row band given

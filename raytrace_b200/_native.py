@@ -85,6 +85,8 @@ SYMBOLS = {
     "vxrt_device_buffer": (C.c_void_p, [_H, C.c_int]),
     "vxrt_cuda_stream": (C.c_void_p, [_H]),
     "vxrt_frame_stats": (C.c_int, [_H, C.POINTER(VxrtFrameStats)]),
+    "vxrt_plan_bands": (C.c_int, [C.c_int, C.c_int, C.c_void_p]),
+    "vxrt_plan_passes": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_void_p]),
     "vxrt_comm_unique_id": (C.c_int, [C.c_void_p, C.c_size_t]),
     "vxrt_comm_init": (C.c_int, [_H, C.c_void_p, C.c_size_t, C.c_int, C.c_int]),
     "vxrt_comm_gather_output": (C.c_int, [_H, C.c_int]),

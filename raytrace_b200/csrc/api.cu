@@ -139,6 +139,37 @@ extern "C" {
 
 int vxrt_abi_version(void) { return VXRT_ABI_VERSION; }
 
+// ---- image-space sharding plan (pure host arithmetic; no device needed) -------------------------------
+int vxrt_plan_bands(int height, int nranks, int32_t* rows) {
+    if (height <= 0 || nranks <= 0 || !rows) return VXRT_ERR_INVALID;
+    // contiguous bands whose edges are multiples of 8 rows (the 8x8 shader group, constants.rs:33)
+    for (int r = 0; r <= nranks; r++) {
+        long long e = (long long)height * r / nranks;
+        e = (e + 7) / 8 * 8;
+        if (e > height || r == nranks) e = height;
+        if (r < nranks) rows[2 * r] = (int32_t)e;
+        if (r > 0) rows[2 * r - 1] = (int32_t)e;
+    }
+    return VXRT_OK;
+}
+
+int vxrt_plan_passes(int height, int row_begin, int row_end, uint32_t flags, int32_t* rows) {
+    if (!rows || height <= 0 || row_begin < 0 || row_end > height || row_begin >= row_end) return VXRT_ERR_INVALID;
+    int halo = 0;
+    if (flags & VXRT_FLAG_DENOISE) for (int k = 0; k < 6; k++) halo += 3 * kDenoiseSizes[k];
+    rows[0] = row_begin - halo < 0 ? 0 : row_begin - halo;
+    rows[1] = row_end + halo > height ? height : row_end + halo;
+    int remaining = halo;
+    for (int k = 0; k < 6; k++) {
+        remaining -= 3 * kDenoiseSizes[k];
+        if (remaining < 0) remaining = 0;
+        int r0 = row_begin - remaining, r1 = row_end + remaining;
+        rows[2 + 2 * k] = r0 < 0 ? 0 : r0;
+        rows[3 + 2 * k] = r1 > height ? height : r1;
+    }
+    return VXRT_OK;
+}
+
 const char* vxrt_last_error(const VxrtHandle* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
 
 int vxrt_create(const VxrtConfig* cfg, VxrtHandle** out) {
@@ -174,10 +205,9 @@ int vxrt_create(const VxrtConfig* cfg, VxrtHandle** out) {
     if (h->cfg.max_steps == 0) h->cfg.max_steps = 2048;      // raytrace.comp:109
     h->row0 = row0; h->row1 = row1;
     // denoise needs 3*size rows of context per pass (bilateral_denoise.comp taps reach +-3*size)
-    int halo = 0;
-    if (cfg->flags & VXRT_FLAG_DENOISE) for (int k = 0; k < 6; k++) halo += 3 * kDenoiseSizes[k];
-    h->trace_row0 = row0 - halo < 0 ? 0 : row0 - halo;
-    h->trace_row1 = row1 + halo > cfg->height ? cfg->height : row1 + halo;
+    vxrt_plan_passes(cfg->height, row0, row1, cfg->flags, h->plan);
+    h->trace_row0 = h->plan[0];
+    h->trace_row1 = h->plan[1];
     h->stream = nullptr;
     for (int i = 0; i < 5; i++) h->ev[i] = nullptr;
     h->d_materials = nullptr; h->d_minefield = nullptr; h->d_noise = nullptr; h->d_lut = nullptr; h->d_dirty = nullptr;
@@ -422,6 +452,7 @@ int vxrt_render_frame(VxrtHandle* h) {
         P.noise_base_y = ((float)t[1] / 255.0f) * 255.0f;
     }
     P.width = h->cfg.width; P.height = h->cfg.height; P.row0 = h->trace_row0; P.row1 = h->trace_row1;
+    P.own_row0 = h->row0; P.own_row1 = h->row1;
     P.nx = h->cfg.nx; P.ny = h->cfg.ny; P.nz = h->cfg.nz;
     P.lx = ilog2(P.nx); P.ly = ilog2(P.ny); P.lz = ilog2(P.nz);
     P.hx = (float)(P.nx / 2); P.hy = (float)(P.ny / 2); P.hz = (float)(P.nz / 2);
@@ -444,13 +475,8 @@ int vxrt_render_frame(VxrtHandle* h) {
     if (h->cfg.flags & VXRT_FLAG_DENOISE) {
         // pipeline.rs:98-115: even passes lighting -> pong, odd passes pong -> lighting.  A band shrinks
         // by 3*size rows per pass towards [row0,row1) so that only valid rows are ever read.
-        int remaining = 0;
-        for (int k = 0; k < 6; k++) remaining += 3 * kDenoiseSizes[k];
         for (int k = 0; k < 6; k++) {
-            remaining -= 3 * kDenoiseSizes[k];
-            int r0 = h->row0 - remaining, r1 = h->row1 + remaining;
-            if (r0 < 0) r0 = 0;
-            if (r1 > h->cfg.height) r1 = h->cfg.height;
+            const int r0 = h->plan[2 + 2 * k], r1 = h->plan[3 + 2 * k];
             const bool odd = (k & 1) != 0;
             const int swap = (odd && (h->cfg.flags & VXRT_FLAG_PONG_SWAP)) ? 1 : 0;
             CU(vxrt_launch_denoise(odd ? h->d_pong : h->d_lighting, odd ? h->d_lighting : h->d_pong, h->d_depth, h->d_normal,

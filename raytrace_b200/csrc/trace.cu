@@ -252,6 +252,7 @@ __global__ void __launch_bounds__(128) k_trace(const __grid_constant__ TracePara
         }
     }
     // frame counters: one atomic per warp and counter
+    if (py < P.own_row0 || py >= P.own_row1) { st.rays = st.steps = st.hits = st.limit = 0; noise_fetches = 0; }   // halo rows: traced, not counted
     uint32_t v[5] = {st.rays, st.steps, st.hits, noise_fetches, st.limit};
 #pragma unroll
     for (int k = 0; k < 5; k++) {

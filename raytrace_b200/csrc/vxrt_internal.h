@@ -19,6 +19,7 @@ struct TraceParams {
     float noise_base_x, noise_base_y;    // raytrace.comp:302-303
     // geometry
     int width, height, row0, row1;       // rows [row0,row1) are traced
+    int own_row0, own_row1;              // rows whose rays enter the frame counters (the band without its halo)
     int nx, ny, nz;                      // window dims (powers of two)
     int lx, ly, lz;                      // log2 of the dims
     float hx, hy, hz;                    // half dims (pos_offset, raytrace.comp:105)
@@ -40,6 +41,7 @@ struct VxrtHandle {
     VxrtConfig cfg;
     int row0, row1;                      // rendered G-buffer rows
     int trace_row0, trace_row1;          // rows traced (band + denoise halo)
+    int32_t plan[14];                    // vxrt_plan_passes: traced rows, then the rows of each denoise pass
     cudaStream_t stream;
     cudaEvent_t ev[5];
     std::string err;
