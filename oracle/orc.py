@@ -204,3 +204,49 @@ def render(materials, minefield, noise, frame_block, mode, width, height, *, den
     if finalize:
         lib().orc_finalize(C.byref(b), _p(fr.lighting), _p(noise), _p(fr.output), r0, r1, threads)
     return fr
+
+
+# ---- oracle/_ref: the reference's own shader text compiled as C++ (oracle/make_ref.py) -------------------
+REF_LIB_PATH = os.path.join(_HERE, "_ref", "libref.so")
+_ref = None
+
+
+def ref_available():
+    return os.path.exists(REF_LIB_PATH)
+
+
+def ref_lib():
+    global _ref
+    if _ref is None:
+        L = C.CDLL(REF_LIB_PATH)
+        L.ref_trace.restype = C.c_int
+        L.ref_trace.argtypes = [C.c_void_p] * 4 + [C.c_int, C.c_int] + [C.c_void_p] * 6 + [C.c_int]
+        L.ref_denoise.restype = C.c_int
+        L.ref_denoise.argtypes = [C.c_void_p] * 4 + [C.c_int] * 4
+        L.ref_finalize.restype = C.c_int
+        L.ref_finalize.argtypes = [C.c_void_p] * 7 + [C.c_int, C.c_int]
+        _ref = L
+    return _ref
+
+
+def ref_render(materials, minefield, noise, frame_block, width, height, *, denoise=True, finalize=True,
+               pong_swap=False, cover_all_rows=True):
+    """The reference's three shaders over a 256^3 window (its compile-time size), full lighting.
+    Returns a Frame holding the G-buffer, lighting_raw, lighting after denoise and the output image."""
+    assert minefield.shape == (256, 256, 256), "the reference shader hard-codes ROOT_BLOCK_WIDTH = 256"
+    fr = Frame(width, height)
+    blk = np.ascontiguousarray(frame_block, np.uint8)
+    L = ref_lib()
+    L.ref_trace(_p(materials), _p(minefield), _p(noise), _p(blk), width, height, _p(fr.lighting), _p(fr.depth),
+                _p(fr.normal), _p(fr.albedo), _p(fr.emission), _p(fr.fog), 1 if cover_all_rows else 0)
+    fr.lighting_raw = fr.lighting.copy()
+    if denoise:
+        pong = np.zeros_like(fr.lighting)
+        for k, size in enumerate(DENOISE_SIZES):
+            src, dst = (fr.lighting, pong) if k % 2 == 0 else (pong, fr.lighting)
+            L.ref_denoise(_p(src), _p(dst), _p(fr.depth), _p(fr.normal), width, height, size,
+                          1 if (pong_swap and k % 2 == 1) else 0)
+    if finalize:
+        L.ref_finalize(_p(fr.albedo), _p(fr.emission), _p(fr.fog), _p(fr.lighting), _p(fr.depth), _p(noise),
+                       _p(fr.output), width, height)
+    return fr

@@ -237,3 +237,30 @@ def test_pipeline_interface(orc, world, noise):
     img2 = pipe.draw_frame(game)
     assert pipe.seed == 2 and not np.array_equal(img1, img2)
     pipe.close()
+
+
+def _golden():
+    import glob, os
+    return sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "*.npz")))
+
+
+@pytest.mark.parametrize("path", _golden(), ids=lambda p: p.split("/")[-1])
+def test_cuda_matches_reference_golden(orc, world, noise, path):
+    """libvxrt against fixtures written by the reference's own shader text (tests/golden/make_golden.py):
+    integer images bit-exact, colour images within the stated tolerance."""
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    g = np.load(path)
+    dims = scenes.WORLDS["mid"][0]
+    m, f = world("mid")
+    H, W = g["depth"].shape
+    flags = N.FLAG_DENOISE | N.FLAG_FINALIZE | N.FLAG_HIT_BUFFERS | (N.FLAG_PONG_SWAP if bool(g["pong_swap"]) else 0)
+    with R.Renderer(W, H, dims, N.MODE_FULL, flags) as r:
+        r.upload_blue_noise(noise); r.upload_world(m, f); r.set_frame(g["frame_block"]); r.render_frame()
+        for buf, name in [(N.BUF_DEPTH, "depth"), (N.BUF_NORMAL, "normal"), (N.BUF_ALBEDO, "albedo"), (N.BUF_EMISSION, "emission")]:
+            assert np.array_equal(r.read_buffer(buf), g[name]), name
+        d = lambda a, b: int(np.max(np.abs(a.astype(np.int64) - b.astype(np.int64))))
+        assert d(r.read_buffer(N.BUF_FOG), g["fog"]) <= C8_TOL
+        assert d(r.read_buffer(N.BUF_LIGHTING_RAW), g["lighting_raw"]) <= C16_TOL
+        assert d(r.read_buffer(N.BUF_LIGHTING), g["lighting"]) <= C16_TOL
+        assert d(r.read_output(), g["output"]) <= C8_TOL
