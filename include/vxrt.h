@@ -40,6 +40,8 @@ typedef enum VxrtMode { VXRT_MODE_PRIMARY = 0, VXRT_MODE_SHADOW = 1, VXRT_MODE_F
 #define VXRT_FLAG_FINALIZE      0x4u  /* run finalize.comp -> RGBA8 output (pipeline.rs:117-123)            */
 #define VXRT_FLAG_ACCUMULATE    0x8u  /* temporal accumulation of `light` (extension)          */
 #define VXRT_FLAG_PONG_SWAP     0x10u /* reproduce descriptor_sets.rs:37-39 (odd passes read swapped images)*/
+#define VXRT_FLAG_GENERAL_MARCH 0x40u /* force the general march kernel (normally chosen per frame when a coordinate
+                                         could reach 2^21 or the window has more than 2^32 voxels)               */
 #define VXRT_FLAG_REF_ROWS      0x20u /* leave the rows the reference grid (W/8,H/8+1) never writes untouched*/
 
 /* Replaces the compile-time constants of src/render/constants.rs:9-10,22-31 and the

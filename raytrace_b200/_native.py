@@ -17,7 +17,7 @@ OK, ERR_INVALID, ERR_CUDA, ERR_STATE, ERR_SIZE, ERR_COMM = 0, -1, -2, -3, -4, -5
 # VxrtMode (truncations of raytrace.comp:main, :320-350)
 MODE_PRIMARY, MODE_SHADOW, MODE_FULL = 0, 1, 2
 # vxrt_create flags
-FLAG_HIT_BUFFERS, FLAG_DENOISE, FLAG_FINALIZE, FLAG_ACCUMULATE, FLAG_PONG_SWAP, FLAG_REF_ROWS = 1, 2, 4, 8, 16, 32
+FLAG_HIT_BUFFERS, FLAG_DENOISE, FLAG_FINALIZE, FLAG_ACCUMULATE, FLAG_PONG_SWAP, FLAG_REF_ROWS, FLAG_GENERAL_MARCH = 1, 2, 4, 8, 16, 32, 64
 # VxrtBufferId
 (BUF_OUTPUT, BUF_LIGHTING, BUF_DEPTH, BUF_NORMAL, BUF_ALBEDO, BUF_EMISSION, BUF_FOG, BUF_HIT_VOXEL, BUF_HIT_FACE,
  BUF_HIT_WORD, BUF_HIT_T, BUF_STEPS, BUF_RAYS, BUF_ACCUM, BUF_LIGHTING_RAW) = range(15)

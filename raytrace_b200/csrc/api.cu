@@ -68,6 +68,20 @@ void diffuse_luts(float* lut) {
     }
 }
 
+// (E8) trace_fast.cu: g(p) = fl(p - lr) is monotone in p, so {p : |g(p)| >= H} = {p <= lo} U {p >= hi}.
+// lo/hi are found by bisection over the floats in their numeric order.
+uint32_t float_key(float f) { uint32_t u; memcpy(&u, &f, 4); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
+float key_float(uint32_t k) { uint32_t u = (k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k; float f; memcpy(&f, &u, 4); return f; }
+void sky_thresholds(float lr, float half, float* lo, float* hi) {
+    auto g = [lr](float p) { volatile float r = p - lr; return (float)r; };
+    uint32_t a = float_key(-3.0e38f), b = float_key(3.0e38f);      // g(a) < H <= g(b)
+    while (b - a > 1) { const uint32_t m = a + (b - a) / 2; if (g(key_float(m)) >= half) b = m; else a = m; }
+    *hi = key_float(b);
+    a = float_key(-3.0e38f); b = float_key(3.0e38f);               // g(a) <= -H < g(b)
+    while (b - a > 1) { const uint32_t m = a + (b - a) / 2; if (g(key_float(m)) <= -half) a = m; else b = m; }
+    *lo = key_float(a);
+}
+
 size_t pixels(const VxrtHandle* h) { return (size_t)h->cfg.width * h->cfg.height; }
 size_t voxels(const VxrtHandle* h) { return (size_t)h->cfg.nx * h->cfg.ny * h->cfg.nz; }
 
@@ -457,6 +471,15 @@ int vxrt_render_frame(VxrtHandle* h) {
     P.lx = ilog2(P.nx); P.ly = ilog2(P.ny); P.lz = ilog2(P.nz);
     P.hx = (float)(P.nx / 2); P.hy = (float)(P.ny / 2); P.hz = (float)(P.nz / 2);
     P.max_steps = h->cfg.max_steps; P.mode = h->cfg.mode; P.flags = h->cfg.flags;
+    {   // preconditions of the instruction-lean march (trace.cu (E5)): every coordinate the march can form stays
+        // below 2^21 in magnitude and texel offsets fit 32 bits; otherwise the general kernel runs
+        const float lim = 2097152.0f;
+        bool ok = P.lx + P.ly + P.lz <= 32 && !(h->cfg.flags & VXRT_FLAG_GENERAL_MARCH);
+        const float o[3] = {P.ox, P.oy, P.oz}, l[3] = {P.lrx, P.lry, P.lrz}, d[3] = {(float)P.nx, (float)P.ny, (float)P.nz};
+        for (int a = 0; a < 3; a++) ok = ok && fabsf(o[a]) + d[a] + 128.0f < lim && fabsf(l[a]) + d[a] + 128.0f < lim;
+        P.fast = ok ? 1 : 0;
+        for (int a = 0; a < 3; a++) sky_thresholds(l[a], d[a] * 0.5f, &P.sky_lo[a], &P.sky_hi[a]);
+    }
     P.minefield = h->d_minefield; P.materials = h->d_materials; P.noise = h->d_noise; P.lut = h->d_lut;
     P.lighting = h->d_lighting; P.depth = h->d_depth; P.normal = h->d_normal; P.albedo = h->d_albedo;
     P.emission = h->d_emission; P.fog = h->d_fog;

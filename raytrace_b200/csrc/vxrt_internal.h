@@ -24,6 +24,8 @@ struct TraceParams {
     int lx, ly, lz;                      // log2 of the dims
     float hx, hy, hz;                    // half dims (pos_offset, raytrace.comp:105)
     int max_steps, mode;
+    int fast;                            // 1: k_trace_fast's preconditions hold for this frame (trace_fast.cu (E5))
+    float sky_lo[3], sky_hi[3];          // (E8): |pos - lr| >= H  <=>  pos <= sky_lo || pos >= sky_hi, per axis
     uint32_t flags;
     float inv_frames;                    // accumulation: 1/(frames so far incl. this one) is NOT used; see k_trace
     // device pointers
@@ -64,7 +66,8 @@ struct VxrtHandle {
 void vxrt_comm_release(VxrtHandle* h);
 
 // launchers (each returns the cudaGetLastError() of its launch)
-cudaError_t vxrt_launch_trace(const TraceParams& p, cudaStream_t s);
+cudaError_t vxrt_launch_trace(const TraceParams& p, cudaStream_t s);        // dispatches on p.fast
+cudaError_t vxrt_launch_trace_fast(const TraceParams& p, cudaStream_t s);
 cudaError_t vxrt_launch_denoise(const ushort4* src, ushort4* dst, const uint16_t* depth, const uint8_t* normal,
                                 int width, int height, int size, int swap, int row0, int row1, cudaStream_t s);
 cudaError_t vxrt_launch_finalize(const uchar4* albedo, const uchar4* emission, const uchar4* fog, const ushort4* lighting,

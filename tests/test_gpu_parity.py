@@ -83,6 +83,66 @@ def test_camera_path_and_render_offset(orc, world, noise):
             _compare(ref, r, N, denoise=True, finalize=True)
 
 
+@pytest.mark.parametrize("general", [False, True], ids=["fast", "general"])
+@pytest.mark.parametrize("case", ["underground", "few_steps", "above_window", "lr_far", "lr_neg", "axis_aligned"])
+def test_edge_rays_both_kernels(orc, world, noise, case, general):
+    """The reference's undefined corners as DESIGN.md D2 defines them, on both march kernels (trace_fast.cu and
+    the general form in trace.cu): camera inside a solid (E4), loop-limit exhaustion, start slid to the -Y
+    face (:312-315), window centres away from 0 (toroidal addressing + (E8) thresholds), axis-aligned rays
+    (a direction component of exactly 0: lpa = inf, (E9))."""
+    import math
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    dims = scenes.WORLDS["mid"][0]
+    m, f = world("mid")
+    cam = scenes.camera(dims)
+    origin, heading, pitch, lr, max_steps = cam["origin"], cam["heading"], cam["pitch"], (0, 0, 0), 2048
+    if case == "underground":
+        origin = (0.5, 0.5, -100.25)
+    elif case == "few_steps":
+        max_steps = 6
+    elif case == "above_window":
+        origin = (3.3, -400.0, 40.7)
+    elif case == "lr_far":
+        lr = (1024, -2048, 512); origin = (origin[0] + 1024, origin[1] - 2048, origin[2] + 512)
+    elif case == "lr_neg":
+        lr = (-48, 16, -32); origin = (origin[0] - 48, origin[1] + 16, origin[2] - 32)
+    elif case == "axis_aligned":
+        heading, pitch = math.pi / 2, 0.0
+    W, H = 136, 72
+    blk = orc.fill_frame(origin, heading, pitch, cam["sun_angle"], 11, lr)
+    ref = orc.render(m, f, noise, blk, 2, W, H, denoise=True, finalize=True, max_steps=max_steps)
+    flags = N.FLAG_HIT_BUFFERS | N.FLAG_DENOISE | N.FLAG_FINALIZE | (N.FLAG_GENERAL_MARCH if general else 0)
+    with R.Renderer(W, H, dims, 2, flags, max_steps=max_steps) as r:
+        r.upload_blue_noise(noise); r.upload_world(m, f); r.set_frame(blk); r.render_frame()
+        _compare(ref, r, N, denoise=True, finalize=True)
+        s = r.frame_stats()
+        assert (s.rays, s.steps, s.hits) == (ref.stats.rays, ref.stats.steps, ref.stats.hits)
+        assert s.limit_exhausted == ref.stats.ub_limit_exhausted
+        if case == "few_steps":
+            assert s.limit_exhausted > 0
+        if case == "underground":
+            assert ref.stats.ub_start_in_solid > 0
+
+
+def test_general_kernel_chosen_far_from_origin(orc, world, noise):
+    """Coordinates beyond 2^21 violate (E5)'s precondition: vxrt_render_frame must fall back to the general
+    kernel by itself, and the result still matches the oracle."""
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    dims = scenes.WORLDS["small"][0]
+    m, f = world("small")
+    cam = scenes.camera(dims)
+    off = (1 << 22)
+    lr = (off, 0, 0)
+    origin = (cam["origin"][0] + off, cam["origin"][1], cam["origin"][2])
+    blk = orc.fill_frame(origin, cam["heading"], cam["pitch"], cam["sun_angle"], 5, lr)
+    ref = orc.render(m, f, noise, blk, 2, 64, 48, denoise=True, finalize=True)
+    with R.Renderer(64, 48, dims, 2, N.FLAG_HIT_BUFFERS | N.FLAG_DENOISE | N.FLAG_FINALIZE) as r:
+        r.upload_blue_noise(noise); r.upload_world(m, f); r.set_frame(blk); r.render_frame()
+        _compare(ref, r, N, denoise=True, finalize=True)
+
+
 def test_pong_swap_flag(orc, world, noise):
     """descriptor_sets.rs:37-39: odd denoise passes read swapped depth/normal images."""
     import raytrace_b200 as R
