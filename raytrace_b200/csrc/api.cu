@@ -474,7 +474,8 @@ int vxrt_render_frame(VxrtHandle* h) {
     {   // preconditions of the instruction-lean march (trace.cu (E5)): every coordinate the march can form stays
         // below 2^21 in magnitude and texel offsets fit 32 bits; otherwise the general kernel runs
         const float lim = 2097152.0f;
-        bool ok = P.lx + P.ly + P.lz <= 32 && !(h->cfg.flags & VXRT_FLAG_GENERAL_MARCH);
+        bool ok = P.lx + P.ly + P.lz <= 32 && !(h->cfg.flags & VXRT_FLAG_GENERAL_MARCH) &&
+                  P.max_steps <= 200000;                  // k_trace_fast packs 5 * max_steps into 20 bits
         const float o[3] = {P.ox, P.oy, P.oz}, l[3] = {P.lrx, P.lry, P.lrz}, d[3] = {(float)P.nx, (float)P.ny, (float)P.nz};
         for (int a = 0; a < 3; a++) ok = ok && fabsf(o[a]) + d[a] + 128.0f < lim && fabsf(l[a]) + d[a] + 128.0f < lim;
         P.fast = ok ? 1 : 0;
