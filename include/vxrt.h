@@ -158,6 +158,16 @@ int  vxrt_reset_accumulation(VxrtHandle* h);
 /* ---- output ------------------------------------------------------------------------- */
 /* replaces queue_present (pipeline.rs:237-254): the frame is a headless device buffer. */
 int  vxrt_read_output(VxrtHandle* h, uint8_t* rgba8, size_t nbytes);
+/* Pipelined read-back (no reference equivalent: the reference presents from the GPU).  The final image is
+ * double-buffered on the device: vxrt_read_output_async enqueues the D2H copy of the frame rendered last on a
+ * second stream and returns a ticket at once, so the next vxrt_render_frame overlaps the copy;
+ * vxrt_wait_output(ticket) blocks until that copy (and every earlier one) has landed in `rgba8`.
+ * The copy only runs at DMA speed when `rgba8` is page-locked: register the caller's buffer once with
+ * vxrt_host_register (cudaHostRegister underneath). */
+int  vxrt_read_output_async(VxrtHandle* h, uint8_t* rgba8, size_t nbytes, uint64_t* ticket);
+int  vxrt_wait_output(VxrtHandle* h, uint64_t ticket);
+int  vxrt_host_register(VxrtHandle* h, void* ptr, size_t nbytes);
+int  vxrt_host_unregister(VxrtHandle* h, void* ptr);
 int  vxrt_read_buffer(VxrtHandle* h, int buffer_id, void* dst, size_t nbytes);
 size_t vxrt_buffer_bytes(const VxrtHandle* h, int buffer_id);
 void* vxrt_device_buffer(VxrtHandle* h, int buffer_id);     /* zero-copy consumers (NCCL gather) */

@@ -80,6 +80,10 @@ SYMBOLS = {
     "vxrt_sync": (C.c_int, [_H]),
     "vxrt_reset_accumulation": (C.c_int, [_H]),
     "vxrt_read_output": (C.c_int, [_H, C.c_void_p, C.c_size_t]),
+    "vxrt_read_output_async": (C.c_int, [_H, C.c_void_p, C.c_size_t, C.POINTER(C.c_uint64)]),
+    "vxrt_wait_output": (C.c_int, [_H, C.c_uint64]),
+    "vxrt_host_register": (C.c_int, [_H, C.c_void_p, C.c_size_t]),
+    "vxrt_host_unregister": (C.c_int, [_H, C.c_void_p]),
     "vxrt_read_buffer": (C.c_int, [_H, C.c_int, C.c_void_p, C.c_size_t]),
     "vxrt_buffer_bytes": (C.c_size_t, [_H, C.c_int]),
     "vxrt_device_buffer": (C.c_void_p, [_H, C.c_int]),

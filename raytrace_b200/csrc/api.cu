@@ -222,7 +222,8 @@ int vxrt_create(const VxrtConfig* cfg, VxrtHandle** out) {
     vxrt_plan_passes(cfg->height, row0, row1, cfg->flags, h->plan);
     h->trace_row0 = h->plan[0];
     h->trace_row1 = h->plan[1];
-    h->stream = nullptr;
+    h->stream = nullptr; h->copy_stream = nullptr; h->out_idx = 0; h->tickets = 0;
+    for (int i = 0; i < 2; i++) { h->ev_frame_done[i] = h->ev_copy_done[i] = nullptr; h->copy_pending[i] = false; h->d_out_buf[i] = nullptr; h->ticket_of_buf[i] = 0; }
     for (int i = 0; i < 5; i++) h->ev[i] = nullptr;
     h->d_materials = nullptr; h->d_minefield = nullptr; h->d_noise = nullptr; h->d_lut = nullptr; h->d_dirty = nullptr;
     h->d_edits = nullptr; h->edits_cap = 0;
@@ -239,6 +240,11 @@ int vxrt_create(const VxrtConfig* cfg, VxrtHandle** out) {
     auto init = [&]() -> int {
         CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
         for (int i = 0; i < 5; i++) CU(cudaEventCreate(&h->ev[i]));
+        CU(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; i++) {
+            CU(cudaEventCreateWithFlags(&h->ev_frame_done[i], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&h->ev_copy_done[i], cudaEventDisableTiming));
+        }
         const size_t V = voxels(h), P = pixels(h);
         int rc;
         if ((rc = alloc_zero(h, (void**)&h->d_materials, V * 4))) return rc;
@@ -257,7 +263,9 @@ int vxrt_create(const VxrtConfig* cfg, VxrtHandle** out) {
         if ((rc = alloc_zero(h, (void**)&h->d_albedo, P * 4))) return rc;
         if ((rc = alloc_zero(h, (void**)&h->d_emission, P * 4))) return rc;
         if ((rc = alloc_zero(h, (void**)&h->d_fog, P * 4))) return rc;
-        if ((rc = alloc_zero(h, (void**)&h->d_output, P * 4))) return rc;
+        if ((rc = alloc_zero(h, (void**)&h->d_out_buf[0], P * 4))) return rc;
+        if ((rc = alloc_zero(h, (void**)&h->d_out_buf[1], P * 4))) return rc;
+        h->d_output = h->d_out_buf[0];
         if (cfg->flags & VXRT_FLAG_DENOISE) if ((rc = alloc_zero(h, (void**)&h->d_pong, P * 8))) return rc;
         if (cfg->flags & VXRT_FLAG_HIT_BUFFERS) {
             if ((rc = alloc_zero(h, (void**)&h->d_hit_voxel, P * 12))) return rc;
@@ -282,12 +290,18 @@ void vxrt_destroy(VxrtHandle* h) {
     if (!h) return;
     cudaSetDevice(h->cfg.device);
     if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
     vxrt_comm_release(h);
     void* ptrs[] = {h->d_materials, h->d_minefield, h->d_noise, h->d_lut, h->d_dirty, h->d_edits, h->d_lighting, h->d_pong,
-                    h->d_lighting_raw, h->d_depth, h->d_normal, h->d_albedo, h->d_emission, h->d_fog, h->d_output,
+                    h->d_lighting_raw, h->d_depth, h->d_normal, h->d_albedo, h->d_emission, h->d_fog, h->d_out_buf[0], h->d_out_buf[1],
                     h->d_hit_voxel, h->d_hit_face, h->d_hit_word, h->d_hit_t, h->d_steps, h->d_rays, h->d_accum, h->d_counters};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 5; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+    for (int i = 0; i < 2; i++) {
+        if (h->ev_frame_done[i]) cudaEventDestroy(h->ev_frame_done[i]);
+        if (h->ev_copy_done[i]) cudaEventDestroy(h->ev_copy_done[i]);
+    }
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -508,6 +522,13 @@ int vxrt_render_frame(VxrtHandle* h) {
         }
     }
     CU(cudaEventRecord(h->ev[2], h->stream));
+    // the image goes to the buffer an asynchronous read-back is not using (vxrt_read_output_async)
+    h->out_idx ^= 1;
+    h->d_output = h->d_out_buf[h->out_idx];
+    if (h->copy_pending[h->out_idx]) {
+        CU(cudaStreamWaitEvent(h->stream, h->ev_copy_done[h->out_idx], 0));
+        h->copy_pending[h->out_idx] = false;
+    }
     if (h->cfg.flags & VXRT_FLAG_FINALIZE)
         CU(vxrt_launch_finalize(h->d_albedo, h->d_emission, h->d_fog, h->d_lighting, h->d_depth, h->d_noise, h->d_output,
                                 h->cfg.width, h->cfg.height, h->row0, h->row1, h->stream));
@@ -544,6 +565,52 @@ int vxrt_read_buffer(VxrtHandle* h, int buffer_id, void* dst, size_t nbytes) {
 }
 
 int vxrt_read_output(VxrtHandle* h, uint8_t* rgba8, size_t nbytes) { return vxrt_read_buffer(h, VXRT_BUF_OUTPUT, rgba8, nbytes); }
+
+int vxrt_read_output_async(VxrtHandle* h, uint8_t* rgba8, size_t nbytes, uint64_t* ticket) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (!rgba8 || !ticket) return fail(h, VXRT_ERR_INVALID, "vxrt_read_output_async: NULL argument");
+    if (!h->rendered) return fail(h, VXRT_ERR_STATE, "vxrt_read_output_async: no frame rendered yet");
+    const size_t bytes = pixels(h) * 4;
+    if (nbytes < bytes) return fail(h, VXRT_ERR_SIZE, "vxrt_read_output_async: host buffer too small");
+    CU(cudaSetDevice(h->cfg.device));
+    const int i = h->out_idx;
+    CU(cudaEventRecord(h->ev_frame_done[i], h->stream));               // everything queued so far (incl. an NCCL gather)
+    CU(cudaStreamWaitEvent(h->copy_stream, h->ev_frame_done[i], 0));
+    CU(cudaMemcpyAsync(rgba8, h->d_out_buf[i], bytes, cudaMemcpyDeviceToHost, h->copy_stream));
+    CU(cudaEventRecord(h->ev_copy_done[i], h->copy_stream));
+    h->copy_pending[i] = true;
+    *ticket = ++h->tickets;
+    h->ticket_of_buf[i] = *ticket;
+    return VXRT_OK;
+}
+
+int vxrt_wait_output(VxrtHandle* h, uint64_t ticket) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (ticket == 0 || ticket > h->tickets) return fail(h, VXRT_ERR_INVALID, "vxrt_wait_output: unknown ticket");
+    CU(cudaSetDevice(h->cfg.device));
+    // copies complete in ticket order on one stream: wait for the oldest recorded copy that is not older than `ticket`
+    int pick = -1;
+    for (int i = 0; i < 2; i++)
+        if (h->ticket_of_buf[i] >= ticket && (pick < 0 || h->ticket_of_buf[i] < h->ticket_of_buf[pick])) pick = i;
+    if (pick >= 0) CU(cudaEventSynchronize(h->ev_copy_done[pick]));
+    return VXRT_OK;
+}
+
+int vxrt_host_register(VxrtHandle* h, void* ptr, size_t nbytes) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (!ptr || !nbytes) return fail(h, VXRT_ERR_INVALID, "vxrt_host_register: NULL or empty buffer");
+    CU(cudaSetDevice(h->cfg.device));
+    CU(cudaHostRegister(ptr, nbytes, cudaHostRegisterPortable));
+    return VXRT_OK;
+}
+
+int vxrt_host_unregister(VxrtHandle* h, void* ptr) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (!ptr) return fail(h, VXRT_ERR_INVALID, "vxrt_host_unregister: NULL");
+    CU(cudaSetDevice(h->cfg.device));
+    CU(cudaHostUnregister(ptr));
+    return VXRT_OK;
+}
 
 int vxrt_frame_stats(VxrtHandle* h, VxrtFrameStats* out) {
     if (!h) return VXRT_ERR_INVALID;

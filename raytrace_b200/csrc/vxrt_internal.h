@@ -46,6 +46,9 @@ struct VxrtHandle {
     int32_t plan[14];                    // vxrt_plan_passes: traced rows, then the rows of each denoise pass
     cudaStream_t stream;
     cudaEvent_t ev[5];
+    // pipelined read-back: the final image is double-buffered so frame k's D2H copy (copy_stream) overlaps frame k+1
+    cudaStream_t copy_stream; cudaEvent_t ev_frame_done[2], ev_copy_done[2]; bool copy_pending[2];
+    uchar4* d_out_buf[2]; int out_idx; unsigned long long tickets, ticket_of_buf[2];
     std::string err;
     // world
     uint32_t* d_materials; uint8_t* d_minefield; uint8_t* d_noise; float* d_lut;
