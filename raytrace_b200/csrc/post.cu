@@ -12,38 +12,67 @@ __device__ __forceinline__ uint32_t unorm_store(float x, float maxv) {
     return __float2uint_rn(fmul(fminf(fmaxf(x, 0.0f), 1.0f), maxv));
 }
 
-// bilateral_denoise.comp:35-89 as a shared-memory tiled kernel.  SWAP reproduces the pong descriptor set
-// (descriptor_sets.rs:37-39: odd passes read the R8 normal image as "depth" and the R16 depth image as
-// "normal").
+// bilateral_denoise.comp:35-89 as a shared-memory tiled, register-sliding kernel.  SWAP reproduces the pong
+// descriptor set (descriptor_sets.rs:37-39: odd passes read the R8 normal image as "depth" and the R16 depth
+// image as "normal").
 //
 // The filter is colour work: its contract is the stated tolerance (<= 1/255 per 8-bit channel after
 // finalize), not bit equality, so this kernel uses FMA contraction, a reciprocal-multiply for the UNORM
-// decode and MUFU.RCP for the 36 weight divisions.  The 16-bit quantisation point after every pass is kept.
+// decode, MUFU.RCP for the 36 weight divisions and its own summation order.  The 16-bit quantisation point
+// after every pass is kept.
 //
 // Tiling: a pass with dilation S only couples pixels whose y differ by multiples of S, so
-// a CTA owns 128 contiguous x (coalesced rows) x TH rows of ONE y-residue class and stages
-// (128 + 6S) x (TH + 6) texels in shared memory, decoded once to {r,g,b,dist} floats + the normal code.
-// Every tap is then one LDS.128 + one LDS.U16 at a compile-time offset; consecutive lanes read consecutive
-// texels (no bank conflicts beyond the 4 wavefronts a 512-byte row needs).
-constexpr int DN_TX = 128;                     // pixels per CTA row (= threads in x)
-template <int S, int TH> struct DnTile {
-    static constexpr int W = DN_TX + 6 * S, R = TH + 6, N = W * R;
+// a CTA owns 128 contiguous x (coalesced rows) x L rows of ONE y-residue class and stages
+// (128 + 6S) x (L + 6) texels in shared memory, decoded once to {r,g,b,dist} floats + the normal code.
+// A thread computes G = 4 vertically adjacent outputs of its column at once: the 10 staged rows they touch are
+// loaded ONCE into registers (58 texels for 4 x 37 taps, i.e. 14.5 shared-memory texel loads per output
+// instead of 37), each texel feeding every output it is a tap of.  The earlier one-output-per-thread form
+// was bound by shared-memory bandwidth (LDS.128 = 4 wavefronts per tap); this one by issue / MUFU.RCP.
+// MUFU.RCP alone (1 ulp-ish): __frcp_rn expands to a 12-instruction IEEE sequence with a slow-path call
+__device__ __forceinline__ float rcp_fast(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+// 16-bit shared load into a 32-bit register: keeps the normal-code comparison a plain 32-bit ISETP (the
+// compiler otherwise narrows it to 16 bits and pays two PRMTs per tap)
+__device__ __forceinline__ uint32_t lds_u16(const uint16_t* p) {
+    uint32_t r;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=r"(r) : "r"((uint32_t)__cvta_generic_to_shared(p)));
+    return r;
+}
+constexpr int DN_TX = 128;                     // pixels per CTA row
+constexpr int DN_TY = 2;                       // thread rows per CTA
+constexpr int DN_G = 4;                        // vertically adjacent outputs per thread
+// decimated rows a thread walks per tile: dilations 1,2,4 / dilations 8,16 (wider x halo -> shorter tile)
+#ifndef VXRT_DN_L0
+#define VXRT_DN_L0 16
+#endif
+#ifndef VXRT_DN_L1
+#define VXRT_DN_L1 8
+#endif
+template <int S, int L> struct DnTile {
+    static constexpr int W = DN_TX + 6 * S, R = L + 6, N = W * R;
     static constexpr size_t BYTES = (size_t)N * (sizeof(float4) + sizeof(uint16_t));
 };
+// SAMPLE list of bilateral_denoise.comp:43-86 as a function of (|dx|, |dy|); 0 = not a tap
+__host__ __device__ constexpr float dn_weight(int ax, int ay) {
+    const int lo = ax < ay ? ax : ay, hi = ax < ay ? ay : ax;
+    return hi == 0 ? 0.146634f
+         : hi == 1 ? (lo == 0 ? 0.092566f : 0.058434f)
+         : hi == 2 ? (lo == 0 ? 0.023205f : lo == 1 ? 0.014648f : 0.003672f)
+         : (lo == 0 ? 0.002289f : lo == 1 ? 0.001445f : 0.0f);
+}
 
-template <int S, int TH, bool SWAP>
-__global__ void __launch_bounds__(256) k_denoise(const ushort4* __restrict__ src, ushort4* __restrict__ dst,
-                                                 const uint16_t* __restrict__ depth, const uint8_t* __restrict__ normal,
-                                                 int width, int height, int row0, int row1, int groups) {
-    using T = DnTile<S, TH>;
+template <int S, int L, bool SWAP>
+__global__ void __launch_bounds__(DN_TX * DN_TY) k_denoise(const ushort4* __restrict__ src, ushort4* __restrict__ dst,
+                                                   const uint16_t* __restrict__ depth, const uint8_t* __restrict__ normal,
+                                                   int width, int height, int row0, int row1, int groups) {
+    using T = DnTile<S, L>;
     extern __shared__ float4 dn_tile[];
     uint16_t* dn_nrm = reinterpret_cast<uint16_t*>(dn_tile + T::N);
     const int tid = threadIdx.y * DN_TX + threadIdx.x;
     const int bx = blockIdx.x * DN_TX;
-    const int res = blockIdx.y / groups, grp = blockIdx.y - res * groups;   // y-residue class, group of TH decimated rows
-    const int ybase = row0 + res + grp * TH * S;                             // G-buffer row of decimated row 0
+    const int res = blockIdx.y / groups, grp = blockIdx.y - res * groups;   // y-residue class, group of L decimated rows
+    const int ybase = row0 + res + grp * L * S;                              // G-buffer row of decimated row 0
     // stage: texel (tx, ty) <- image (clamp(bx + tx - 3S), clamp(ybase + (ty - 3) * S))   (sampleAt, :14-21)
-    for (int e = tid; e < T::N; e += 256) {
+    for (int e = tid; e < T::N; e += DN_TX * DN_TY) {
         const int ty = e / T::W, tx = e - ty * T::W;
         const int gx = min(max(bx + tx - 3 * S, 0), width - 1), gy = min(max(ybase + (ty - 3) * S, 0), height - 1);
         const size_t gi = (size_t)gy * width + gx;
@@ -56,59 +85,85 @@ __global__ void __launch_bounds__(256) k_denoise(const ushort4* __restrict__ src
     __syncthreads();
     const int x = bx + threadIdx.x;
     if (x >= width) return;
+    const int c0 = threadIdx.x + 3 * S;                    // this thread's column in the tile
 #pragma unroll 1
-    for (int j = threadIdx.y; j < TH; j += 2) {
-        const int y = ybase + j * S;
-        if (y >= row1) break;
-        const int c = (j + 3) * T::W + threadIdx.x + 3 * S;
-        const size_t pi = (size_t)y * width + x;
-        const uint32_t cn = dn_nrm[c];
-        if (cn >= 16) { dst[pi] = __ldg(src + pi); continue; }                 // :88-89
-        const float4 cv = dn_tile[c];
-        float tw = 0.146634f;                                                  // :41
-        float sr = cv.x * tw, sg = cv.y * tw, sb = cv.z * tw;
-#define DN_TAP(DX, DY, WGT)                                                                       \
-        {                                                                                         \
-            const int o = c + (DY) * T::W + (DX) * S;                                             \
-            const float4 q = dn_tile[o];                                                          \
-            const float den = fmaf(4.0f, fabsf(cv.w - q.w), dn_nrm[o] == cn ? 1.0f : 11.0f);      \
-            const float w = (WGT) * __frcp_rn(den);                                               \
-            tw += w; sr = fmaf(q.x, w, sr); sg = fmaf(q.y, w, sg); sb = fmaf(q.z, w, sb);         \
+    for (int o0 = threadIdx.y * DN_G; o0 < L; o0 += DN_TY * DN_G) {       // outputs o0 .. o0+G-1 (decimated rows)
+        if (ybase + o0 * S >= row1) break;
+        float tw[DN_G], sr[DN_G], sg[DN_G], sb[DN_G], cd[DN_G];
+        uint32_t cn[DN_G];
+#pragma unroll
+        for (int k = 0; k < DN_G; k++) {                   // centre of output k is staged row o0 + k + 3
+            cd[k] = dn_tile[(o0 + k + 3) * T::W + c0].w;
+            cn[k] = lds_u16(dn_nrm + (o0 + k + 3) * T::W + c0);
+            tw[k] = 0.0f; sr[k] = 0.0f; sg[k] = 0.0f; sb[k] = 0.0f;
         }
-        // SAMPLE list, bilateral_denoise.comp:43-86, source order
-        DN_TAP(0, 1, 0.092566f) DN_TAP(0, -1, 0.092566f) DN_TAP(1, 0, 0.092566f) DN_TAP(-1, 0, 0.092566f)
-        DN_TAP(1, 1, 0.058434f) DN_TAP(-1, 1, 0.058434f) DN_TAP(-1, -1, 0.058434f) DN_TAP(1, -1, 0.058434f)
-        DN_TAP(2, 0, 0.023205f) DN_TAP(-2, 0, 0.023205f) DN_TAP(0, 2, 0.023205f) DN_TAP(0, -2, 0.023205f)
-        DN_TAP(2, 2, 0.003672f) DN_TAP(-2, 2, 0.003672f) DN_TAP(-2, -2, 0.003672f) DN_TAP(2, -2, 0.003672f)
-        DN_TAP(2, 1, 0.014648f) DN_TAP(-2, 1, 0.014648f) DN_TAP(-2, -1, 0.014648f) DN_TAP(2, -1, 0.014648f)
-        DN_TAP(1, 2, 0.014648f) DN_TAP(-1, 2, 0.014648f) DN_TAP(-1, -2, 0.014648f) DN_TAP(1, -2, 0.014648f)
-        DN_TAP(3, 0, 0.002289f) DN_TAP(-3, 0, 0.002289f) DN_TAP(0, 3, 0.002289f) DN_TAP(0, -3, 0.002289f)
-        DN_TAP(3, 1, 0.001445f) DN_TAP(-3, 1, 0.001445f) DN_TAP(-3, -1, 0.001445f) DN_TAP(3, -1, 0.001445f)
-        DN_TAP(1, 3, 0.001445f) DN_TAP(-1, 3, 0.001445f) DN_TAP(-1, -3, 0.001445f) DN_TAP(1, -3, 0.001445f)
-#undef DN_TAP
-        const float inv = __frcp_rn(tw);
-        dst[pi] = make_ushort4((unsigned short)unorm_store(sr * inv, 65535.0f), (unsigned short)unorm_store(sg * inv, 65535.0f),
-                               (unsigned short)unorm_store(sb * inv, 65535.0f), 65535);   // :87
+#pragma unroll
+        for (int rho = 0; rho < DN_G + 6; rho++) {         // staged row o0 + rho is tap row dy = rho - 3 - k of output k
+            // widest tap row any of the G outputs needs from this staged row
+            int wmax = 0;
+#pragma unroll
+            for (int k = 0; k < DN_G; k++) {
+                const int dy = rho - 3 - k, ay = dy < 0 ? -dy : dy;
+                const int wd = ay <= 1 ? 3 : ay == 2 ? 2 : ay == 3 ? 1 : 0;
+                wmax = wd > wmax ? wd : wmax;
+            }
+#pragma unroll
+            for (int dx = -3; dx <= 3; dx++) {
+                if (dx < -wmax || dx > wmax) continue;
+                const float4 t = dn_tile[(o0 + rho) * T::W + c0 + dx * S];
+                const uint32_t tn = lds_u16(dn_nrm + (o0 + rho) * T::W + c0 + dx * S);
+#pragma unroll
+                for (int k = 0; k < DN_G; k++) {
+                    const int dy = rho - 3 - k;
+                    if (dy < -3 || dy > 3) continue;
+                    const float wgt = dn_weight(dx < 0 ? -dx : dx, dy < 0 ? -dy : dy);
+                    if (wgt == 0.0f) continue;
+                    float w;
+                    if (dx == 0 && dy == 0) {
+                        w = wgt;                                               // :41 centre tap, no bilateral term
+                    } else {
+                        // w = wgt / (4|dc - dq| + (nq == nc ? 0 : 10) + 1)   (:23-33), one reciprocal of the scaled sum
+                        const float pen = (tn == cn[k]) ? (1.0f / wgt) : (11.0f / wgt);
+                        w = rcp_fast(fmaf(4.0f / wgt, fabsf(cd[k] - t.w), pen));
+                    }
+                    tw[k] += w; sr[k] = fmaf(t.x, w, sr[k]); sg[k] = fmaf(t.y, w, sg[k]); sb[k] = fmaf(t.z, w, sb[k]);
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < DN_G; k++) {
+            const int y = ybase + (o0 + k) * S;
+            if (y >= row1) break;
+            const size_t pi = (size_t)y * width + x;
+            if (cn[k] >= 16) {
+                dst[pi] = __ldg(src + pi);                                     // :88-89
+            } else {
+                const float inv = rcp_fast(tw[k]);
+                dst[pi] = make_ushort4((unsigned short)unorm_store(sr[k] * inv, 65535.0f), (unsigned short)unorm_store(sg[k] * inv, 65535.0f),
+                                       (unsigned short)unorm_store(sb[k] * inv, 65535.0f), 65535);   // :87
+            }
+        }
     }
 }
 
-template <int S, int TH>
+template <int S, int L>
 cudaError_t launch_denoise_s(const ushort4* src, ushort4* dst, const uint16_t* depth, const uint8_t* normal, int width,
                              int height, int swap, int row0, int row1, cudaStream_t s) {
-    using T = DnTile<S, TH>;
+    using T = DnTile<S, L>;
     const int rows = row1 - row0;
     const int per_res = (rows + S - 1) / S;                 // decimated rows of the fullest residue class
-    const int groups = (per_res + TH - 1) / TH;
-    dim3 grid((width + DN_TX - 1) / DN_TX, S * groups), block(DN_TX, 2);
+    const int groups = (per_res + L - 1) / L;
+    dim3 grid((width + DN_TX - 1) / DN_TX, S * groups), block(DN_TX, DN_TY);
+    static_assert(L % DN_G == 0, "tile height must be a multiple of the outputs per thread");
     static bool attr_set = false;                           // per template instantiation
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(k_denoise<S, TH, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T::BYTES);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_denoise<S, TH, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T::BYTES);
+        cudaError_t e = cudaFuncSetAttribute(k_denoise<S, L, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T::BYTES);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_denoise<S, L, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T::BYTES);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    if (swap) k_denoise<S, TH, true><<<grid, block, T::BYTES, s>>>(src, dst, depth, normal, width, height, row0, row1, groups);
-    else k_denoise<S, TH, false><<<grid, block, T::BYTES, s>>>(src, dst, depth, normal, width, height, row0, row1, groups);
+    if (swap) k_denoise<S, L, true><<<grid, block, T::BYTES, s>>>(src, dst, depth, normal, width, height, row0, row1, groups);
+    else k_denoise<S, L, false><<<grid, block, T::BYTES, s>>>(src, dst, depth, normal, width, height, row0, row1, groups);
     return cudaGetLastError();
 }
 
@@ -158,11 +213,11 @@ cudaError_t vxrt_launch_denoise(const ushort4* src, ushort4* dst, const uint16_t
                                 int width, int height, int size, int swap, int row0, int row1, cudaStream_t s) {
     if (row1 <= row0) return cudaSuccess;
     switch (size) {                                        // pipeline.rs:103: sizes 1, 2, 4, 8, 8, 16
-        case 1: return launch_denoise_s<1, 16>(src, dst, depth, normal, width, height, swap, row0, row1, s);
-        case 2: return launch_denoise_s<2, 16>(src, dst, depth, normal, width, height, swap, row0, row1, s);
-        case 4: return launch_denoise_s<4, 16>(src, dst, depth, normal, width, height, swap, row0, row1, s);
-        case 8: return launch_denoise_s<8, 8>(src, dst, depth, normal, width, height, swap, row0, row1, s);
-        case 16: return launch_denoise_s<16, 8>(src, dst, depth, normal, width, height, swap, row0, row1, s);
+        case 1: return launch_denoise_s<1, VXRT_DN_L0>(src, dst, depth, normal, width, height, swap, row0, row1, s);
+        case 2: return launch_denoise_s<2, VXRT_DN_L0>(src, dst, depth, normal, width, height, swap, row0, row1, s);
+        case 4: return launch_denoise_s<4, VXRT_DN_L0>(src, dst, depth, normal, width, height, swap, row0, row1, s);
+        case 8: return launch_denoise_s<8, VXRT_DN_L1>(src, dst, depth, normal, width, height, swap, row0, row1, s);
+        case 16: return launch_denoise_s<16, VXRT_DN_L1>(src, dst, depth, normal, width, height, swap, row0, row1, s);
         default: return cudaErrorInvalidValue;
     }
 }
