@@ -13,6 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libvxrt.so")
+HOST_OUT = os.path.join(HERE, "vxrt_main")
 SOURCES = ["api.cu", "trace.cu", "trace_fast.cu", "post.cu", "world.cu", "comm.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-ffp-contract=off,-fno-fast-math", "-shared"]
@@ -26,10 +27,12 @@ def _nvcc():
 
 
 def needs_build():
-    if not os.path.exists(OUT):
+    if not os.path.exists(OUT) or not os.path.exists(HOST_OUT):
         return True
-    t = os.path.getmtime(OUT)
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "vxrt.h")]
+    t = min(os.path.getmtime(OUT), os.path.getmtime(HOST_OUT))
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h"))]
+    deps += [os.path.join(CSRC, "host", f) for f in os.listdir(os.path.join(CSRC, "host"))]
+    deps = deps + [os.path.join(HERE, "..", "include", "vxrt.h")]
     return any(os.path.getmtime(d) > t for d in deps)
 
 
@@ -44,7 +47,21 @@ def build(force=False, verbose=False):
         sys.stderr.write(r.stdout)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed building libvxrt.so")
+    build_host(verbose)
     return OUT
+
+
+def build_host(verbose=False):
+    """C++ host driver above the C ABI (csrc/host/: the reference's render/game/world interfaces + a headless
+    src/bin/main.rs), linked against the in-tree libvxrt.so."""
+    cmd = ["g++", "-O2", "-std=c++17", "-ffp-contract=off", "-I", os.path.join(HERE, "..", "include"), "-o", HOST_OUT,
+           os.path.join(CSRC, "host", "vxrt_main.cpp"), "-L", HERE, "-lvxrt", "-Wl,-rpath,$ORIGIN"]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if verbose or r.returncode != 0:
+        sys.stderr.write(r.stdout)
+    if r.returncode != 0:
+        raise RuntimeError("g++ failed building vxrt_main")
+    return HOST_OUT
 
 
 if __name__ == "__main__":

@@ -85,3 +85,17 @@ def test_argument_validation_without_device():
     assert N.lib.vxrt_create(None, C.byref(h)) == N.ERR_INVALID
     assert N.lib.vxrt_render_frame(None) == N.ERR_INVALID
     N.lib.vxrt_destroy(None)
+
+
+@pytest.mark.skipif(os.path.exists("/dev/nvidiactl"), reason="needs a machine WITHOUT a GPU")
+def test_cpp_host_driver_fails_loudly_without_device(tmp_path):
+    """csrc/host/vxrt_main (the C++ caller of the ABI) must surface VXRT_ERR_CUDA, not render on the CPU."""
+    import subprocess
+    import numpy as np
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "raytrace_b200", "vxrt_main")
+    assert os.path.exists(exe), "vxrt_main not built (raytrace_b200/build.py)"
+    (tmp_path / "w.u32").write_bytes(np.zeros(64 ** 3, np.uint32).tobytes())
+    (tmp_path / "n.rgba").write_bytes(np.zeros(512 * 512 * 4, np.uint8).tobytes())
+    p = subprocess.run([exe, "--world", str(tmp_path / "w.u32"), "--noise", str(tmp_path / "n.rgba"), "--dims", "64", "64", "64",
+                        "--size", "64", "64"], capture_output=True, text=True, timeout=60)
+    assert p.returncode == 1 and "libvxrt error -2" in p.stderr and "no CUDA device" in p.stderr

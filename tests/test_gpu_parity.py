@@ -355,3 +355,34 @@ def test_cuda_matches_reference_golden(orc, world, noise, path):
         assert d(r.read_buffer(N.BUF_LIGHTING_RAW), g["lighting_raw"]) <= C16_TOL
         assert d(r.read_buffer(N.BUF_LIGHTING), g["lighting"]) <= C16_TOL
         assert d(r.read_output(), g["output"]) <= C8_TOL
+
+
+def test_cpp_host_driver(orc, world, noise, tmp_path):
+    """The C++ host side (csrc/host/: Game -> create_instance -> draw_frame, a headless src/bin/main.rs)
+    uploads the world chunk by chunk with no minefield (built on the device), renders, and its frame is
+    checked against the oracle fed with the uniform block the driver itself filled."""
+    import os, subprocess
+    from raytrace_b200 import scenes
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "raytrace_b200", "vxrt_main")
+    assert os.path.exists(exe), "vxrt_main not built (raytrace_b200/build.py)"
+    dims = scenes.WORLDS["c1"][0]
+    m, f = world("c1")
+    cam = scenes.camera(dims)
+    (tmp_path / "w.u32").write_bytes(np.ascontiguousarray(m).tobytes())
+    (tmp_path / "n.rgba").write_bytes(np.ascontiguousarray(noise).tobytes())
+    W, H = 192, 136
+    cmd = [exe, "--world", str(tmp_path / "w.u32"), "--noise", str(tmp_path / "n.rgba"), "--dims", *map(str, dims),
+           "--size", str(W), str(H), "--frames", "3", "--hold", "forward", "--dt", "0.05", "--mode", "2",
+           "--camera", *[repr(float(v)) for v in (*cam["origin"], cam["heading"], cam["pitch"], cam["sun_angle"])],
+           "--out", str(tmp_path / "o.ppm"), "--block", str(tmp_path / "b.bin")]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=120)
+    assert p.returncode == 0, p.stderr
+    assert "Creating renderer" in p.stdout and "ms /" in p.stdout
+    blk = np.frombuffer((tmp_path / "b.bin").read_bytes(), np.uint8)
+    assert blk.size == 192 and int(blk[4:8].view(np.uint32)[0]) == 3          # seed pre-incremented per frame
+    raw = (tmp_path / "o.ppm").read_bytes()
+    hdr = f"P6\n{W} {H}\n255\n".encode()
+    assert raw.startswith(hdr)
+    img = np.frombuffer(raw[len(hdr):], np.uint8).reshape(H, W, 3)
+    ref = orc.render(m, f, noise, blk, 2, W, H, denoise=True, finalize=True)
+    assert np.max(np.abs(img.astype(int) - ref.output[..., :3].astype(int))) <= C8_TOL
