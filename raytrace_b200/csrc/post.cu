@@ -38,11 +38,14 @@ __device__ __forceinline__ uint32_t lds_u16(const uint16_t* p) {
     return r;
 }
 constexpr int DN_TX = 128;                     // pixels per CTA row
-constexpr int DN_TY = 2;                       // thread rows per CTA
+#ifndef VXRT_DN_TY
+#define VXRT_DN_TY 2
+#endif
+constexpr int DN_TY = VXRT_DN_TY;              // thread rows per CTA
 constexpr int DN_G = 4;                        // vertically adjacent outputs per thread
 // decimated rows a thread walks per tile: dilations 1,2,4 / dilations 8,16 (wider x halo -> shorter tile)
 #ifndef VXRT_DN_L0
-#define VXRT_DN_L0 16
+#define VXRT_DN_L0 8
 #endif
 #ifndef VXRT_DN_L1
 #define VXRT_DN_L1 8
@@ -71,6 +74,29 @@ __global__ void __launch_bounds__(DN_TX * DN_TY) k_denoise(const ushort4* __rest
     const int bx = blockIdx.x * DN_TX;
     const int res = blockIdx.y / groups, grp = blockIdx.y - res * groups;   // y-residue class, group of L decimated rows
     const int ybase = row0 + res + grp * L * S;                              // G-buffer row of decimated row 0
+    const int x = bx + threadIdx.x;
+    // Pixels whose normal code is >= 16 (sky) are plain copies (:88-89).  A tile with no other pixel skips the
+    // staging and the taps altogether; the result is the same image.
+    {
+        bool work = false;
+        if (x < width)
+            for (int o = threadIdx.y * DN_G; o < L; o += DN_TY * DN_G)
+#pragma unroll
+                for (int k = 0; k < DN_G; k++) {
+                    const int y = ybase + (o + k) * S;
+                    if (y < row1) { const size_t pi = (size_t)y * width + x; work |= (SWAP ? (uint32_t)__ldg(depth + pi) : (uint32_t)__ldg(normal + pi)) < 16u; }
+                }
+        if (!__syncthreads_or(work)) {
+            if (x < width)
+                for (int o = threadIdx.y * DN_G; o < L; o += DN_TY * DN_G)
+#pragma unroll
+                    for (int k = 0; k < DN_G; k++) {
+                        const int y = ybase + (o + k) * S;
+                        if (y < row1) { const size_t pi = (size_t)y * width + x; dst[pi] = __ldg(src + pi); }
+                    }
+            return;
+        }
+    }
     // stage: texel (tx, ty) <- image (clamp(bx + tx - 3S), clamp(ybase + (ty - 3) * S))   (sampleAt, :14-21)
     for (int e = tid; e < T::N; e += DN_TX * DN_TY) {
         const int ty = e / T::W, tx = e - ty * T::W;
@@ -83,7 +109,6 @@ __global__ void __launch_bounds__(DN_TX * DN_TY) k_denoise(const ushort4* __rest
         dn_nrm[e] = (uint16_t)(SWAP ? d : n);
     }
     __syncthreads();
-    const int x = bx + threadIdx.x;
     if (x >= width) return;
     const int c0 = threadIdx.x + 3 * S;                    // this thread's column in the tile
 #pragma unroll 1
@@ -96,6 +121,17 @@ __global__ void __launch_bounds__(DN_TX * DN_TY) k_denoise(const ushort4* __rest
             cd[k] = dn_tile[(o0 + k + 3) * T::W + c0].w;
             cn[k] = lds_u16(dn_nrm + (o0 + k + 3) * T::W + c0);
             tw[k] = 0.0f; sr[k] = 0.0f; sg[k] = 0.0f; sb[k] = 0.0f;
+        }
+        bool sky = true;
+#pragma unroll
+        for (int k = 0; k < DN_G; k++) sky &= cn[k] >= 16;
+        if (__all_sync(__activemask(), sky)) {             // the warp's 32 x 4 outputs are all copies
+#pragma unroll
+            for (int k = 0; k < DN_G; k++) {
+                const int y = ybase + (o0 + k) * S;
+                if (y < row1) { const size_t pi = (size_t)y * width + x; dst[pi] = __ldg(src + pi); }
+            }
+            continue;
         }
 #pragma unroll
         for (int rho = 0; rho < DN_G + 6; rho++) {         // staged row o0 + rho is tap row dy = rho - 3 - k of output k
@@ -169,13 +205,15 @@ cudaError_t launch_denoise_s(const ushort4* src, ushort4* dst, const uint16_t* d
 
 // finalize.comp:21-31
 __device__ __forceinline__ float filmic_curve(float x) {
-    if (x < 0.3f) return fmul(x, x);
-    else if (x < 1.13333f) return fsub(fmul(x, 0.6f), 0.09f);
-    else if (x < 2.5f) return fsub(1.0f, fmul(fmul(0.219512195116f, fsub(x, 2.5f)), fsub(x, 2.5f)));
+    if (x < 0.3f) return x * x;
+    else if (x < 1.13333f) return fmaf(x, 0.6f, -0.09f);
+    else if (x < 2.5f) return fmaf(-0.219512195116f * (x - 2.5f), x - 2.5f, 1.0f);
     else return 1.0f;
 }
 
-// finalize.comp:33-64
+// finalize.comp:33-64.  Colour work under the tolerance contract (<= 1/255 per channel): UNORM decodes are
+// reciprocal multiplies folded into the constants, FMA contraction allowed (the IEEE-division form spent ~480
+// instructions per pixel and was issue-bound; this one is bound by its 30 B/pixel of traffic).
 __global__ void __launch_bounds__(256) k_finalize(const uchar4* __restrict__ albedo, const uchar4* __restrict__ emission,
                                                   const uchar4* __restrict__ fog, const ushort4* __restrict__ lighting,
                                                   const uint16_t* __restrict__ depth, const uint8_t* __restrict__ noise,
@@ -183,26 +221,21 @@ __global__ void __launch_bounds__(256) k_finalize(const uchar4* __restrict__ alb
     const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = row0 + blockIdx.y * 8 + (threadIdx.x >> 5);
     if (x >= width || y >= row1) return;
     const size_t pi = (size_t)y * width + x;
-    const uchar4 a = albedo[pi], e = emission[pi], f = fog[pi];
-    const ushort4 l = lighting[pi];
-    const uint32_t d = depth[pi];
-    const uchar4 bn = reinterpret_cast<const uchar4*>(noise)[(y & 511) * VXRT_NOISE_SIZE + (x & 511)];   // :55-57
-    float fog_amount = fdiv((float)d, 32.0f * 128.0f * 8.0f);                  // :47
-    if (fog_amount > 1.0f) fog_amount = 1.0f;
+    const uchar4 a = __ldg(albedo + pi), e = __ldg(emission + pi), f = __ldg(fog + pi);
+    const ushort4 l = __ldg(lighting + pi);
+    const uint32_t d = __ldg(depth + pi);
+    const uchar4 bn = __ldg(reinterpret_cast<const uchar4*>(noise) + (y & 511) * VXRT_NOISE_SIZE + (x & 511));   // :55-57
+    const float fog_amount = fminf((float)d * (1.0f / (32.0f * 128.0f * 8.0f)), 1.0f);   // :47-48
     const float av[3] = {(float)a.x, (float)a.y, (float)a.z}, ev[3] = {(float)e.x, (float)e.y, (float)e.z},
                 fv[3] = {(float)f.x, (float)f.y, (float)f.z}, lv[3] = {(float)l.x, (float)l.y, (float)l.z},
                 nv[3] = {(float)bn.x, (float)bn.y, (float)bn.z};
     uint32_t o[3];
 #pragma unroll
     for (int k = 0; k < 3; k++) {
-        float v = fadd(fmul(fdiv(av[k], 255.0f), fmul(fdiv(lv[k], 65535.0f), 16.0f)), fmul(fdiv(ev[k], 255.0f), 4.0f));   // :36-40
-        if (d < 0xFFFF) {                                                      // :44-50
-            const float fg = fmul(fdiv(fv[k], 255.0f), 2.0f);
-            v = fadd(fmul(v, fsub(1.0f, fog_amount)), fmul(fg, fog_amount));
-        }
-        v = filmic_curve(v);
-        v = fadd(v, fdiv(fdiv(nv[k], 255.0f), 128.0f));                        // :58
-        o[k] = unorm_store(v, 255.0f);
+        float v = fmaf(av[k] * lv[k], 16.0f / (255.0f * 65535.0f), ev[k] * (4.0f / 255.0f));   // :36-40
+        if (d < 0xFFFF) v = fmaf(fv[k] * (2.0f / 255.0f) - v, fog_amount, v);                    // :44-50 mix(v, fog*2, amount)
+        v = fmaf(nv[k], 1.0f / (255.0f * 128.0f), filmic_curve(v));                               // :52-58
+        o[k] = __float2uint_rn(__saturatef(v) * 255.0f);
     }
     out[(size_t)(height - y - 1) * width + x] = make_uchar4((unsigned char)o[0], (unsigned char)o[1], (unsigned char)o[2], 255);   // :60-63
 }
