@@ -46,6 +46,9 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=4)
     ap.add_argument("--impl", default="vxrt", choices=["vxrt", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--comm", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: peer = halo rows and output bands stored over NVLink peer memory by our own kernels (peer.cu); "
+                         "nccl = every band re-traces its denoise halo, NCCL send/recv gathers the bands (comm.cu)")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the bounded oracle timing on rank 0")
     ap.add_argument("--no-l2-flush", action="store_true", help="do not flush L2 between timed steps")
     return ap.parse_args()
@@ -182,7 +185,11 @@ def run_vxrt(args, rank, world_size, local_rank):
     r.upload_blue_noise(noise)
     r.generate_world(kind, seed)                 # world replicated: every rank generates the same seeded world
     lib, h = N.lib, r.handle
-    if world_size > 1:
+    if world_size > 1 and args.comm == "peer":
+        blobs = [None] * world_size
+        dist.all_gather_object(blobs, r.peer_export())       # 512-byte CUDA IPC blobs over the host channel, once
+        r.peer_attach(blobs, rank, root=0)
+    elif world_size > 1:
         ident = [None]
         if rank == 0:
             buf = (C.c_uint8 * N.COMM_ID_BYTES)()
@@ -208,7 +215,7 @@ def run_vxrt(args, rank, world_size, local_rank):
     def step(i):
         r.set_frame(blocks[i])
         r.render_frame()
-        if world_size > 1:
+        if world_size > 1 and args.comm == "nccl":
             r._check(lib.vxrt_comm_gather_output(h, 0))
 
     # ---- device-resident timing: per-step CUDA events on the handle's stream, L2 flushed between steps ----
@@ -288,7 +295,9 @@ def run_vxrt(args, rank, world_size, local_rank):
             "frames_per_s": args.steps / (dev_ms / 1e3), "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": desc, "mode": MODE_NAMES[mode], "width": W, "height": H, "world": list(dims),
-                       "passes": "trace + 6 denoise + finalize" + (" + NCCL band gather" if world_size > 1 else ""),
+                       "passes": "trace + 6 denoise + finalize" + ("" if world_size == 1 else " + NCCL band gather (bands re-trace their halo)"
+                                                                   if args.comm == "nccl" else
+                                                                   " (halo rows pushed / bands stored into the root image over NVLink peer memory)"),
                        "parallelism": f"image row bands x{world_size}, world replicated",
                        "l2": "inputs 640 MiB > L2, not flushed" if flush is None else "flushed between steps (256 MiB fill, untimed)"},
             "rays_per_frame": rays / args.steps, "mean_steps_per_ray": steps_total / max(rays, 1.0),
@@ -298,7 +307,8 @@ def run_vxrt(args, rank, world_size, local_rank):
             "trace_mrays_per_s_rank0": tot["rays"] / trace_s / 1e6,
             "e2e": {"value": rays / e2e_s / 1e6, "unit": "Mrays/s", "frames_per_s": args.steps / e2e_s,
                     "h2d_bytes_per_step": 192, "d2h_bytes_per_step": W * H * 4},
-            "gpu_launches": args.steps * 8 * world_size,
+            # per frame and rank: k_trace, 6 k_denoise, k_finalize; peer mode adds k_halo_push + 3 k_peer_sync (+1 on the root)
+            "gpu_launches": args.steps * (8 * world_size + ((4 * world_size + 1) if world_size > 1 and args.comm == "peer" else 0)),
             "roofline": {"kernel": "k_trace", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
                          "algo_bytes_per_launch": tot["algo"] / args.steps, "launch_ms": tot["trace_ms"] / args.steps,

@@ -196,6 +196,21 @@ int  vxrt_comm_gather_output(VxrtHandle* h, int root);
 /* Broadcast root's host edit list (n given on every rank) and apply it on every replica. */
 int  vxrt_comm_broadcast_edits(VxrtHandle* h, const VxrtEdit* edits, size_t n, int root);
 
+
+/* ---- multi-GPU frame over NVLink peer memory (no NCCL on the per-frame path; peer.cu) ---------------------
+ * After vxrt_peer_attach a band traces only its own rows: the rows of lighting/depth/normal a neighbour's
+ * denoise needs are stored straight into that neighbour's images, the final RGBA8 band is stored by the
+ * finalize kernel straight into the root's output image, and ordering is by frame counters in device memory.
+ * Every rank must call vxrt_render_frame the same number of times.  Ranks may be processes (CUDA IPC) or
+ * handles of one process.
+ *   1. every rank: vxrt_peer_export(h, blob)          (VXRT_PEER_BLOB_BYTES bytes)
+ *   2. all-gather the blobs by any host channel (rank order)
+ *   3. every rank: vxrt_peer_attach(h, blobs, nranks * VXRT_PEER_BLOB_BYTES, rank, nranks, root)
+ * The root's vxrt_read_output / vxrt_read_output_async then return the whole frame. */
+#define VXRT_PEER_BLOB_BYTES 512
+int  vxrt_peer_export(VxrtHandle* h, void* blob, size_t nbytes);
+int  vxrt_peer_attach(VxrtHandle* h, const void* blobs, size_t nbytes, int rank, int nranks, int root);
+
 #ifdef __cplusplus
 }
 #endif

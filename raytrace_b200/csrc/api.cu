@@ -292,6 +292,7 @@ void vxrt_destroy(VxrtHandle* h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
     vxrt_comm_release(h);
+    vxrt_peer_release(h);
     void* ptrs[] = {h->d_materials, h->d_minefield, h->d_noise, h->d_lut, h->d_dirty, h->d_edits, h->d_lighting, h->d_pong,
                     h->d_lighting_raw, h->d_depth, h->d_normal, h->d_albedo, h->d_emission, h->d_fog, h->d_out_buf[0], h->d_out_buf[1],
                     h->d_hit_voxel, h->d_hit_face, h->d_hit_word, h->d_hit_t, h->d_steps, h->d_rays, h->d_accum, h->d_counters};
@@ -503,10 +504,16 @@ int vxrt_render_frame(VxrtHandle* h) {
     P.accum = h->d_accum;
     P.counters = h->d_counters;
 
+    // the image goes to the buffer an asynchronous read-back is not using (vxrt_read_output_async)
+    h->out_idx ^= 1;
+    h->d_output = h->d_out_buf[h->out_idx];
+    int prc;
+    if (h->peer_on && (prc = vxrt_peer_begin_frame(h, h->out_idx))) return prc;
     CU(cudaMemsetAsync(h->d_counters, 0, 8 * sizeof(unsigned long long), h->stream));
     CU(cudaEventRecord(h->ev[0], h->stream));
     CU(vxrt_launch_trace(P, h->stream));
     CU(cudaEventRecord(h->ev[1], h->stream));
+    if (h->peer_on && (prc = vxrt_peer_exchange_halo(h))) return prc;       // rows the neighbours' denoise needs (peer.cu)
     if (h->d_lighting_raw)
         CU(cudaMemcpyAsync(h->d_lighting_raw, h->d_lighting, pixels(h) * 8, cudaMemcpyDeviceToDevice, h->stream));
     if (h->d_accum) h->frames_accumulated++;
@@ -521,17 +528,17 @@ int vxrt_render_frame(VxrtHandle* h) {
                                    h->cfg.width, h->cfg.height, kDenoiseSizes[k], swap, r0, r1, h->stream));
         }
     }
+    if (h->peer_on && (prc = vxrt_peer_after_denoise(h))) return prc;
     CU(cudaEventRecord(h->ev[2], h->stream));
-    // the image goes to the buffer an asynchronous read-back is not using (vxrt_read_output_async)
-    h->out_idx ^= 1;
-    h->d_output = h->d_out_buf[h->out_idx];
     if (h->copy_pending[h->out_idx]) {
         CU(cudaStreamWaitEvent(h->stream, h->ev_copy_done[h->out_idx], 0));
         h->copy_pending[h->out_idx] = false;
     }
     if (h->cfg.flags & VXRT_FLAG_FINALIZE)
-        CU(vxrt_launch_finalize(h->d_albedo, h->d_emission, h->d_fog, h->d_lighting, h->d_depth, h->d_noise, h->d_output,
+        CU(vxrt_launch_finalize(h->d_albedo, h->d_emission, h->d_fog, h->d_lighting, h->d_depth, h->d_noise,
+                                h->peer_on ? vxrt_peer_output(h, h->out_idx) : h->d_output,       // peer mode: straight into the root's image
                                 h->cfg.width, h->cfg.height, h->row0, h->row1, h->stream));
+    if (h->peer_on && (prc = vxrt_peer_end_frame(h))) return prc;
     CU(cudaEventRecord(h->ev[3], h->stream));
     h->rendered = true;
     return VXRT_OK;
@@ -620,6 +627,9 @@ int vxrt_frame_stats(VxrtHandle* h, VxrtFrameStats* out) {
     unsigned long long c[8];
     CU(cudaMemcpyAsync(c, h->d_counters, sizeof c, cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
+    uint32_t perr = 0;
+    { const int rc = vxrt_peer_error_word(h, &perr); if (rc) return rc; }
+    if (perr) return fail(h, VXRT_ERR_COMM, "peer-memory frame: a wait on another rank's flag timed out (ranks out of step?)");
     out->rays = c[0]; out->steps = c[1]; out->hits = c[2]; out->noise_fetches = c[3]; out->limit_exhausted = c[4];
     CU(cudaEventElapsedTime(&out->trace_ms, h->ev[0], h->ev[1]));
     CU(cudaEventElapsedTime(&out->denoise_ms, h->ev[1], h->ev[2]));

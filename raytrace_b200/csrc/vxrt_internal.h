@@ -7,6 +7,8 @@
 #include "../../include/vxrt.h"
 
 #define VXRT_NOISE_SIZE 512
+#define VXRT_PEER_MAX_RANKS 16
+#define VXRT_PEER_MAX_LINKS 16
 #define VXRT_CHUNK 64
 
 // Per-frame constants handed to the kernels by value (fits the 4 KB parameter space).
@@ -39,6 +41,9 @@ struct TraceParams {
     unsigned long long* counters;        // [0]=rays [1]=steps [2]=hits [3]=noise fetches [4]=limit exhausted
 };
 
+// one halo link of the peer-memory frame (peer.cu): rows [r0,r1) go to / come from `rank`
+struct VxrtPeerLink { int rank, r0, r1; void *lighting, *depth, *normal; };
+
 struct VxrtHandle {
     VxrtConfig cfg;
     int row0, row1;                      // rendered G-buffer rows
@@ -65,8 +70,23 @@ struct VxrtHandle {
     uint32_t frames_accumulated;
     // multi-GPU (comm.cu)
     void* comm; int rank, nranks; std::vector<int32_t> bands;   // bands[2r], bands[2r+1] = rows of rank r
+    // multi-GPU over peer memory (peer.cu)
+    bool peer_on = false; int peer_root = 0; uint32_t peer_frame = 0;
+    uint32_t* d_peer_flags = nullptr;                            // this handle's flag words (exported)
+    std::vector<uint32_t*> peer_flags;                           // every rank's flag words as seen from this device
+    std::vector<VxrtPeerLink> peer_dst, peer_src;
+    void* peer_root_out[2] = {nullptr, nullptr};                 // the root's two output images
+    std::vector<void*> peer_ipc_opened;
+    cudaStream_t peer_stream = nullptr; cudaEvent_t ev_peer = nullptr;
 };
 void vxrt_comm_release(VxrtHandle* h);
+void vxrt_peer_release(VxrtHandle* h);
+int vxrt_peer_begin_frame(VxrtHandle* h, int out_idx);
+int vxrt_peer_exchange_halo(VxrtHandle* h);
+int vxrt_peer_after_denoise(VxrtHandle* h);
+uchar4* vxrt_peer_output(VxrtHandle* h, int out_idx);
+int vxrt_peer_end_frame(VxrtHandle* h);
+int vxrt_peer_error_word(VxrtHandle* h, uint32_t* out);
 
 // launchers (each returns the cudaGetLastError() of its launch)
 cudaError_t vxrt_launch_trace(const TraceParams& p, cudaStream_t s);        // dispatches on p.fast

@@ -386,3 +386,57 @@ def test_cpp_host_driver(orc, world, noise, tmp_path):
     img = np.frombuffer(raw[len(hdr):], np.uint8).reshape(H, W, 3)
     ref = orc.render(m, f, noise, blk, 2, W, H, denoise=True, finalize=True)
     assert np.max(np.abs(img.astype(int) - ref.output[..., :3].astype(int))) <= C8_TOL
+
+
+@pytest.mark.parametrize("bands", [[(0, 136), (136, 264), (264, 400)], [(0, 56), (56, 112), (112, 200), (200, 400)]],
+                         ids=["3_bands", "4_bands_thinner_than_halo"])
+def test_peer_memory_frame_matches_single_handle(orc, world, noise, bands):
+    """The multi-GPU frame of peer.cu (own-rows trace, halo rows pushed into the neighbours' images, finalize
+    storing straight into the root's output, flag-ordered) with every band as a handle of THIS process on one GPU:
+    the root's image must equal the single-handle frame bit for bit, over several frames (both output parities,
+    back-pressure flags) and through the pipelined read-back."""
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    dims = scenes.WORLDS["c1"][0]
+    m, f = world("c1")
+    W, H = 160, 400
+    flags = N.FLAG_DENOISE | N.FLAG_FINALIZE
+    blocks = [_frame_block(orc, dims, seed=s) for s in (5, 6, 7, 8)]
+    want = []
+    with R.Renderer(W, H, dims, 2, flags) as full:
+        full.upload_blue_noise(noise); full.upload_world(m, f)
+        for b in blocks:
+            full.set_frame(b); full.render_frame(); want.append(full.read_output().copy())
+    rs = [R.Renderer(W, H, dims, 2, flags, rows=b) for b in bands]
+    try:
+        for r in rs:
+            r.upload_blue_noise(noise); r.upload_world(m, f)
+        blobs = [r.peer_export() for r in rs]
+        root = 1
+        for k, r in enumerate(rs):
+            r.peer_attach(blobs, k, root=root)
+        host = [np.zeros((H, W, 4), np.uint8) for _ in range(2)]
+        for b in host:
+            rs[root].host_register(b)
+        tickets = []
+        for i, b in enumerate(blocks):
+            for r in rs:                                   # enqueue only: no rank may block the host before all have queued
+                r.set_frame(b); r.render_frame()
+            if i < 2:
+                assert np.array_equal(rs[root].read_output(), want[i]), f"frame {i}"
+            else:                                          # pipelined read-back of frames 2 and 3
+                tickets.append(rs[root].read_output_async(host[i & 1]))
+        for t in tickets:
+            rs[root].wait_output(t)
+        assert np.array_equal(host[0], want[2]) and np.array_equal(host[1], want[3])
+        for b in host:
+            rs[root].host_unregister(b)
+        for r in rs:
+            r.sync(); r.frame_stats()                      # raises VXRT_ERR_COMM if a flag wait timed out
+        rays = sum(r.frame_stats().rays for r in rs)
+        with R.Renderer(W, H, dims, 2, flags) as full:
+            full.upload_blue_noise(noise); full.upload_world(m, f); full.set_frame(blocks[-1]); full.render_frame()
+            assert rays == full.frame_stats().rays         # no band traced a halo row
+    finally:
+        for r in rs:
+            r.close()
