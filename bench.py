@@ -49,6 +49,9 @@ def parse_args():
     ap.add_argument("--comm", default="peer", choices=["peer", "nccl"],
                     help="N > 1: peer = halo rows and output bands stored over NVLink peer memory by our own kernels (peer.cu); "
                          "nccl = every band re-traces its denoise halo, NCCL send/recv gathers the bands (comm.cu)")
+    ap.add_argument("--bands", default="balanced", choices=["balanced", "equal"],
+                    help="N > 1: balanced = row bands from per-row work counters of three calibration frames "
+                         "(vxrt_plan_bands_weighted); equal = equal-height bands")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the bounded oracle timing on rank 0")
     ap.add_argument("--no-l2-flush", action="store_true", help="do not flush L2 between timed steps")
     return ap.parse_args()
@@ -161,7 +164,7 @@ def run_reference(args, rank, world_size):
             "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
             "note": "reference GLSL/Vulkan path cannot run on this box; this is the CPU restatement (oracle/) with OpenMP"}
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 def run_vxrt(args, rank, world_size, local_rank):
@@ -178,10 +181,24 @@ def run_vxrt(args, rank, world_size, local_rank):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     scene, W, H, mode, n_path, accumulate, desc = WORKLOADS[args.workload]
     dims, kind, seed = scenes.WORLDS[scene]
-    band = R.plan_bands(H, world_size)[rank]
     flags = N.FLAG_DENOISE | N.FLAG_FINALIZE | (N.FLAG_ACCUMULATE if accumulate else 0)
-    r = R.Renderer(W, H, dims, mode, flags, device=local_rank, rows=band if world_size > 1 else None)
     noise = R.world.default_blue_noise()
+    from oracle import orc                        # only the source of the seeded camera blocks, exactly as tests/ use it
+    bands = [(0, H)]
+    if world_size > 1 and args.bands == "balanced":
+        # Load-balanced bands (setup, untimed): every rank renders three frames of the path on a full-frame handle,
+        # sums the per-row work counters and runs the same deterministic plan, so no rank needs to be told its rows.
+        with R.Renderer(W, H, dims, mode, (flags | N.FLAG_HIT_BUFFERS) & ~N.FLAG_ACCUMULATE, device=local_rank) as cal:
+            cal.upload_blue_noise(noise); cal.generate_world(kind, seed)
+            tc, dc = np.zeros(H, np.float32), np.zeros(H, np.float32)
+            for k in sorted({0, n_path // 2, n_path - 1}):
+                cal.set_frame(frame_blocks(orc, dims, n_path, n_path)[k]); cal.render_frame()
+                t, d = cal.row_costs(); tc += t; dc += d
+        bands = R.plan_bands_weighted(H, world_size, tc, dc, flags)
+    elif world_size > 1:
+        bands = R.plan_bands(H, world_size)
+    band = bands[rank]
+    r = R.Renderer(W, H, dims, mode, flags, device=local_rank, rows=band if world_size > 1 else None)
     r.upload_blue_noise(noise)
     r.generate_world(kind, seed)                 # world replicated: every rank generates the same seeded world
     lib, h = N.lib, r.handle
@@ -198,9 +215,7 @@ def run_vxrt(args, rank, world_size, local_rank):
         dist.broadcast_object_list(ident, src=0)
         r._check(lib.vxrt_comm_init(h, ident[0], N.COMM_ID_BYTES, rank, world_size))
 
-    # frame blocks: host-side parameter fill (pipeline.rs:191-207); the oracle module is only the source of
-    # the seeded camera blocks here, exactly as tests/ use it
-    from oracle import orc
+    # frame blocks: host-side parameter fill (pipeline.rs:191-207)
     n_frames = args.warmup + args.steps
     blocks = frame_blocks(orc, dims, n_path, n_frames)
     stream = torch.cuda.ExternalStream(r.cuda_stream(), device=torch.device("cuda", local_rank))
@@ -299,6 +314,7 @@ def run_vxrt(args, rank, world_size, local_rank):
                                                                    if args.comm == "nccl" else
                                                                    " (halo rows pushed / bands stored into the root image over NVLink peer memory)"),
                        "parallelism": f"image row bands x{world_size}, world replicated",
+                       "bands": [list(b) for b in bands],
                        "l2": "inputs 640 MiB > L2, not flushed" if flush is None else "flushed between steps (256 MiB fill, untimed)"},
             "rays_per_frame": rays / args.steps, "mean_steps_per_ray": steps_total / max(rays, 1.0),
             "limit_exhausted": limit,
@@ -321,13 +337,26 @@ def run_vxrt(args, rank, world_size, local_rank):
             t, cr = time_oracle(orc, (m, f), noise, blocks[args.warmup:], mode, W, H, nb, 1, accumulate)
             line["cpu_baseline"] = {"value": cr / t / 1e6, "unit": "Mrays/s", "frames_per_s": nb / t, "cores": os.cpu_count(),
                                     "kind": "port", "sample": f"{nb} full frames of the same workload through the oracle (OpenMP)"}
-        print(json.dumps(line), flush=True)
+        _emit(line)
     r.close()
     if dist is not None:
         dist.destroy_process_group()
 
 
+def _emit(line):
+    """The ONE JSON line goes to the real stdout; everything else libraries print (e.g. NCCL's version banner)
+    was redirected to stderr in main()."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world_size = int(os.environ.get("WORLD_SIZE", "1"))

@@ -178,6 +178,15 @@ int  vxrt_frame_stats(VxrtHandle* h, VxrtFrameStats* out);  /* syncs the stream 
 /* rows[2r], rows[2r+1] = band [begin,end) of rank r: contiguous, edges on multiples of 8 rows
  * (the 8x8 shader group, constants.rs:33). */
 int  vxrt_plan_bands(int height, int nranks, int32_t* rows /* 2*nranks */);
+/* Load-balanced variant: contiguous bands (edges on multiples of 8 rows) that equalise the modelled cost of a band,
+ * its denoise halo included.  trace_cost[y] / denoise_cost[y] (per pass) are per-row costs in march-step units as
+ * vxrt_row_costs returns them for a representative frame (sky rows are cheap, ground rows are not: equal-height
+ * bands leave the rank that owns the ground with most of the work). */
+int  vxrt_plan_bands_weighted(int height, int nranks, uint32_t flags, const float* trace_cost, const float* denoise_cost,
+                              int32_t* rows /* 2*nranks */);
+/* Per-row cost of the frame rendered last (needs VXRT_FLAG_HIT_BUFFERS): trace_cost[y] = steps + 7 rays + 16.7 W,
+ * denoise_cost[y] = 15 filtered pixels + 0.45 W; rows outside the handle's band read 0. */
+int  vxrt_row_costs(VxrtHandle* h, float* trace_cost, float* denoise_cost, size_t n);
 /* For a handle rendering [row_begin,row_end): rows[0..1] = rows the trace pass must cover (band + 117-row
  * denoise halo, clipped), rows[2+2k..3+2k] = rows denoise pass k (sizes 1,2,4,8,8,16, pipeline.rs:103)
  * must cover so that the final band only ever read valid rows. */

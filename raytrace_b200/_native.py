@@ -90,6 +90,8 @@ SYMBOLS = {
     "vxrt_cuda_stream": (C.c_void_p, [_H]),
     "vxrt_frame_stats": (C.c_int, [_H, C.POINTER(VxrtFrameStats)]),
     "vxrt_plan_bands": (C.c_int, [C.c_int, C.c_int, C.c_void_p]),
+    "vxrt_plan_bands_weighted": (C.c_int, [C.c_int, C.c_int, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "vxrt_row_costs": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_size_t]),
     "vxrt_plan_passes": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_void_p]),
     "vxrt_comm_unique_id": (C.c_int, [C.c_void_p, C.c_size_t]),
     "vxrt_comm_init": (C.c_int, [_H, C.c_void_p, C.c_size_t, C.c_int, C.c_int]),

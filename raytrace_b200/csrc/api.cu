@@ -184,6 +184,56 @@ int vxrt_plan_passes(int height, int row_begin, int row_end, uint32_t flags, int
     return VXRT_OK;
 }
 
+// Load-balanced bands.  Cost model in units of one march step (from the ncu instruction counts of r1: 47
+// instructions per step, ~330 per ray, ~560 per pixel of the trace pass; ~375 per filtered pixel and pass of the
+// denoise at 2/3 of the trace pass's issue rate; ~220 per pixel of finalize + copies):
+//   trace(row)          = steps + 7 rays + 12 W
+//   denoise(row, pass)  = 15 filtered + 0.45 W
+//   finalize(row)       = 4.7 W
+// A band also filters its halo rows: a row at distance d outside the band is filtered by every pass whose
+// remaining halo (114, 108, 96, 72, 48, 0 rows after passes 1..6) still reaches it.
+int vxrt_plan_bands_weighted(int height, int nranks, uint32_t flags, const float* trace_cost, const float* denoise_cost, int32_t* rows) {
+    if (height <= 0 || nranks <= 0 || !rows || !trace_cost || !denoise_cost) return VXRT_ERR_INVALID;
+    if (nranks == 1) { rows[0] = 0; rows[1] = height; return VXRT_OK; }
+    const bool dn = (flags & VXRT_FLAG_DENOISE) != 0;
+    std::vector<double> pt(height + 1, 0.0), pd(height + 1, 0.0);
+    for (int y = 0; y < height; y++) { pt[y + 1] = pt[y] + trace_cost[y]; pd[y + 1] = pd[y] + (dn ? denoise_cost[y] : 0.0); }
+    auto sum = [&](const std::vector<double>& p, int a, int b) { a = a < 0 ? 0 : a; b = b > height ? height : b; return a < b ? p[b] - p[a] : 0.0; };
+    int reach[6]; { int rem = 0; for (int k = 0; k < 6; k++) rem += 3 * kDenoiseSizes[k]; for (int k = 0; k < 6; k++) { rem -= 3 * kDenoiseSizes[k]; reach[k] = rem; } }
+    auto cost = [&](int a, int b) {
+        double c = sum(pt, a, b) + 6.0 * sum(pd, a, b);
+        if (dn) for (int k = 0; k < 6; k++) c += sum(pd, a - reach[k], a) + sum(pd, b, b + reach[k]);
+        return c;
+    };
+    // smallest T such that greedy bands of cost <= T (edges on multiples of 8 rows) cover the frame
+    auto cover = [&](double T, int32_t* out) {
+        int a = 0;
+        for (int r = 0; r < nranks; r++) {
+            int b = a + 8 > height ? height : a + 8;                  // a band has at least one 8-row group
+            if (r == nranks - 1) b = height;
+            else while (b < height && cost(a, b + 8 > height ? height : b + 8) <= T) b = b + 8 > height ? height : b + 8;
+            // leave at least 8 rows for every later rank
+            const int max_b = height - 8 * (nranks - 1 - r);
+            if (b > max_b) b = max_b;
+            if (b <= a) return false;
+            if (out) { out[2 * r] = a; out[2 * r + 1] = b; }
+            a = b;
+        }
+        return true;
+    };
+    if (height < 8 * nranks) return VXRT_ERR_INVALID;
+    double lo = 0.0, hi = cost(0, height);
+    std::vector<int32_t> tmp(2 * nranks);
+    for (int it = 0; it < 60; it++) {
+        const double T = 0.5 * (lo + hi);
+        cover(T, tmp.data());
+        const double last = cost(tmp[2 * (nranks - 1)], height);     // the last band takes whatever is left
+        if (last <= T) hi = T; else lo = T;
+    }
+    cover(hi, rows);
+    return VXRT_OK;
+}
+
 const char* vxrt_last_error(const VxrtHandle* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
 
 int vxrt_create(const VxrtConfig* cfg, VxrtHandle** out) {
@@ -616,6 +666,29 @@ int vxrt_host_unregister(VxrtHandle* h, void* ptr) {
     if (!ptr) return fail(h, VXRT_ERR_INVALID, "vxrt_host_unregister: NULL");
     CU(cudaSetDevice(h->cfg.device));
     CU(cudaHostUnregister(ptr));
+    return VXRT_OK;
+}
+
+int vxrt_row_costs(VxrtHandle* h, float* trace_cost, float* denoise_cost, size_t n) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (!trace_cost || !denoise_cost || n < (size_t)h->cfg.height) return fail(h, VXRT_ERR_SIZE, "vxrt_row_costs: need height floats per array");
+    if (!h->rendered) return fail(h, VXRT_ERR_STATE, "vxrt_row_costs: no frame rendered yet");
+    if (!h->d_steps) return fail(h, VXRT_ERR_STATE, "vxrt_row_costs: the handle needs VXRT_FLAG_HIT_BUFFERS");
+    CU(cudaSetDevice(h->cfg.device));
+    const int H = h->cfg.height, W = h->cfg.width;
+    float* d = nullptr;
+    CU(cudaMalloc((void**)&d, (size_t)H * 3 * sizeof(float)));
+    std::vector<float> v((size_t)H * 3);
+    cudaError_t e = vxrt_launch_row_cost(h->d_steps, h->d_rays, h->d_normal, W, H, d, h->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(v.data(), d, v.size() * sizeof(float), cudaMemcpyDeviceToHost, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    cudaFree(d);
+    CU(e);
+    for (int y = 0; y < H; y++) {
+        const bool own = y >= h->row0 && y < h->row1;                 // rows this handle did not render cost nothing here
+        trace_cost[y] = own ? v[3 * y] + 7.0f * v[3 * y + 1] + 12.0f * W + 4.7f * W : 0.0f;
+        denoise_cost[y] = own ? 15.0f * v[3 * y + 2] + 0.45f * W : 0.0f;
+    }
     return VXRT_OK;
 }
 

@@ -240,7 +240,33 @@ __global__ void __launch_bounds__(256) k_finalize(const uchar4* __restrict__ alb
     out[(size_t)(height - y - 1) * width + x] = make_uchar4((unsigned char)o[0], (unsigned char)o[1], (unsigned char)o[2], 255);   // :60-63
 }
 
+// Per-row work counters of the last frame for the load-balanced band plan (vxrt_plan_bands_weighted): march
+// steps, trace_ray calls and pixels the denoise filters (normal code < 16).  One CTA per row.
+__global__ void __launch_bounds__(256) k_row_cost(const uint32_t* __restrict__ steps, const uint8_t* __restrict__ rays,
+                                                  const uint8_t* __restrict__ normal, int width, float* __restrict__ out) {
+    const int y = blockIdx.x;
+    unsigned long long s = 0; uint32_t r = 0, n = 0;
+    for (int x = threadIdx.x; x < width; x += 256) {
+        const size_t pi = (size_t)y * width + x;
+        s += steps[pi]; r += rays[pi]; n += normal[pi] < 16 ? 1u : 0u;
+    }
+    __shared__ unsigned long long ss[256]; __shared__ uint32_t sr[256], sn[256];
+    ss[threadIdx.x] = s; sr[threadIdx.x] = r; sn[threadIdx.x] = n;
+    __syncthreads();
+    for (int k = 128; k > 0; k >>= 1) {
+        if (threadIdx.x < k) { ss[threadIdx.x] += ss[threadIdx.x + k]; sr[threadIdx.x] += sr[threadIdx.x + k]; sn[threadIdx.x] += sn[threadIdx.x + k]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { out[3 * y] = (float)ss[0]; out[3 * y + 1] = (float)sr[0]; out[3 * y + 2] = (float)sn[0]; }
+}
+
 }  // namespace
+
+cudaError_t vxrt_launch_row_cost(const uint32_t* steps, const uint8_t* rays, const uint8_t* normal, int width, int height,
+                                 float* out, cudaStream_t s) {
+    k_row_cost<<<height, 256, 0, s>>>(steps, rays, normal, width, out);
+    return cudaGetLastError();
+}
 
 cudaError_t vxrt_launch_denoise(const ushort4* src, ushort4* dst, const uint16_t* depth, const uint8_t* normal,
                                 int width, int height, int size, int swap, int row0, int row1, cudaStream_t s) {

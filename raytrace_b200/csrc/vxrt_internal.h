@@ -96,6 +96,8 @@ cudaError_t vxrt_launch_denoise(const ushort4* src, ushort4* dst, const uint16_t
 cudaError_t vxrt_launch_finalize(const uchar4* albedo, const uchar4* emission, const uchar4* fog, const ushort4* lighting,
                                  const uint16_t* depth, const uint8_t* noise, uchar4* out, int width, int height,
                                  int row0, int row1, cudaStream_t s);
+cudaError_t vxrt_launch_row_cost(const uint32_t* steps, const uint8_t* rays, const uint8_t* normal, int width, int height,
+                                 float* out /* 3 per row: steps, rays, filtered pixels */, cudaStream_t s);
 cudaError_t vxrt_launch_build_minefield(uint32_t* materials, uint8_t* minefield, int nx, int ny, int nz,
                                         const uint32_t* dirty /*NULL = all chunks*/, cudaStream_t s);
 cudaError_t vxrt_launch_apply_edits(uint32_t* materials, uint32_t* dirty, const VxrtEdit* d_edits, size_t n,

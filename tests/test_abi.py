@@ -99,3 +99,24 @@ def test_cpp_host_driver_fails_loudly_without_device(tmp_path):
     p = subprocess.run([exe, "--world", str(tmp_path / "w.u32"), "--noise", str(tmp_path / "n.rgba"), "--dims", "64", "64", "64",
                         "--size", "64", "64"], capture_output=True, text=True, timeout=60)
     assert p.returncode == 1 and "libvxrt error -2" in p.stderr and "no CUDA device" in p.stderr
+
+
+def test_plan_bands_weighted():
+    """Pure host arithmetic: bands tile the frame on 8-row edges; cheap (sky) rows make wider bands; uniform cost
+    gives the edge ranks (one denoise halo instead of two) the taller bands."""
+    import numpy as np
+    import raytrace_b200 as R
+    H = 1080
+    t = np.full(H, 100.0, np.float32); d = np.full(H, 10.0, np.float32)
+    for n in (1, 2, 3, 4, 8):
+        b = R.plan_bands_weighted(H, n, t, d)
+        assert b[0][0] == 0 and b[-1][1] == H and all(b[i][1] == b[i + 1][0] for i in range(n - 1))
+        assert all(lo % 8 == 0 for lo, _ in b) and all(hi > lo for lo, hi in b)
+    b = R.plan_bands_weighted(H, 8, t, d)
+    assert b[0][1] - b[0][0] > b[3][1] - b[3][0] and b[7][1] - b[7][0] > b[4][1] - b[4][0]
+    t[:400] = 10.0; d[:400] = 0.5                                 # rows 0..399 nearly free
+    b = R.plan_bands_weighted(H, 2, t, d)
+    assert b[0][1] > 650
+    assert R.plan_bands_weighted(64, 8, t[:64], d[:64]) == [(8 * i, 8 * i + 8) for i in range(8)]
+    with pytest.raises(R.VxrtError):
+        R.plan_bands_weighted(32, 8, t[:32], d[:32])              # fewer than 8 rows per rank

@@ -440,3 +440,40 @@ def test_peer_memory_frame_matches_single_handle(orc, world, noise, bands):
     finally:
         for r in rs:
             r.close()
+
+
+def test_row_costs_and_balanced_bands(orc, world, noise):
+    """vxrt_row_costs against numpy on the hit buffers; the weighted plan gives the sky-heavy part of the frame the
+    taller band, and a peer-memory frame over those bands still equals the single-handle frame."""
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    dims = scenes.WORLDS["c1"][0]
+    m, f = world("c1")
+    W, H = 160, 400
+    flags = N.FLAG_DENOISE | N.FLAG_FINALIZE
+    blk = _frame_block(orc, dims, seed=5)
+    with R.Renderer(W, H, dims, 2, flags | N.FLAG_HIT_BUFFERS) as full:
+        full.upload_blue_noise(noise); full.upload_world(m, f); full.set_frame(blk); full.render_frame()
+        want = full.read_output().copy()
+        t, d = full.row_costs()
+        steps = full.read_buffer(N.BUF_STEPS).astype(np.float64).sum(1)
+        rays = full.read_buffer(N.BUF_RAYS).astype(np.float64).sum(1)
+        filt = (full.read_buffer(N.BUF_NORMAL) < 16).sum(1)
+    assert np.allclose(t, steps + 7 * rays + 16.7 * W, rtol=1e-5) and np.allclose(d, 15 * filt + 0.45 * W, rtol=1e-5)
+    bands = R.plan_bands_weighted(H, 3, t, d, flags)
+    cost = [t[a:b].sum() + 6 * d[a:b].sum() for a, b in bands]
+    eq = [t[a:b].sum() + 6 * d[a:b].sum() for a, b in R.plan_bands(H, 3)]
+    assert max(cost) < max(eq)                                 # better balanced than equal-height bands
+    rs = [R.Renderer(W, H, dims, 2, flags, rows=b) for b in bands]
+    try:
+        for r in rs:
+            r.upload_blue_noise(noise); r.upload_world(m, f)
+        blobs = [r.peer_export() for r in rs]
+        for k, r in enumerate(rs):
+            r.peer_attach(blobs, k, root=0)
+        for r in rs:
+            r.set_frame(blk); r.render_frame()
+        assert np.array_equal(rs[0].read_output(), want)
+    finally:
+        for r in rs:
+            r.close()
