@@ -245,6 +245,11 @@ def run_vxrt(args, rank, world_size, local_rank):
         if flush is not None:
             with torch.cuda.stream(stream):
                 flush.fill_(k & 0xFF)            # evicts L2 (126 MB) — untimed, before the step's start event
+        if world_size > 1:                       # align the ranks (untimed): a rank that starts late would otherwise
+            if args.comm == "peer":              # put its L2 flush inside its neighbours' timed region
+                r.peer_barrier()                 # device-side barrier on the handle's stream (peer.cu)
+            else:
+                torch.cuda.synchronize(); dist.barrier()
         ev[k][0].record(stream)
         step(args.warmup + k)
         ev[k][1].record(stream)
@@ -295,6 +300,12 @@ def run_vxrt(args, rank, world_size, local_rank):
         dist.all_reduce(sums, op=dist.ReduceOp.SUM)
     dev_ms, e2e_s, wall = vals.tolist()
     rays, steps_total, hits, algo, limit = sums.tolist()
+    mine = {"trace": tot["trace_ms"] / args.steps, "denoise": tot["denoise_ms"] / args.steps, "finalize": tot["finalize_ms"] / args.steps,
+            "rows": list(band)}
+    per_rank = [mine]
+    if dist is not None:
+        per_rank = [None] * world_size
+        dist.all_gather_object(per_rank, mine)
     if rank == 0:
         peaks = {}
         try:
@@ -320,6 +331,7 @@ def run_vxrt(args, rank, world_size, local_rank):
             "limit_exhausted": limit,
             "kernel_ms_per_step_rank0": {"trace": tot["trace_ms"] / args.steps, "denoise": tot["denoise_ms"] / args.steps,
                                           "finalize": tot["finalize_ms"] / args.steps},
+            "kernel_ms_per_step_by_rank": per_rank,
             "trace_mrays_per_s_rank0": tot["rays"] / trace_s / 1e6,
             "e2e": {"value": rays / e2e_s / 1e6, "unit": "Mrays/s", "frames_per_s": args.steps / e2e_s,
                     "h2d_bytes_per_step": 192, "d2h_bytes_per_step": W * H * 4},

@@ -219,6 +219,9 @@ int  vxrt_comm_broadcast_edits(VxrtHandle* h, const VxrtEdit* edits, size_t n, i
 #define VXRT_PEER_BLOB_BYTES 512
 int  vxrt_peer_export(VxrtHandle* h, void* blob, size_t nbytes);
 int  vxrt_peer_attach(VxrtHandle* h, const void* blobs, size_t nbytes, int rank, int nranks, int root);
+/* Device-side barrier over all ranks, enqueued on the handle's stream (no host round trip): benchmarks use it to
+ * align the ranks before a timed frame. */
+int  vxrt_peer_barrier(VxrtHandle* h);
 
 #ifdef __cplusplus
 }

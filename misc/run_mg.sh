@@ -17,3 +17,10 @@ for f in sorted(glob.glob("gpurun_out/${tag}_n*.json")):
         d=json.load(open(f)); print(f, "Mrays/s %.0f fps %.0f ms %.4f e2e fps %.0f"%(d["value"], d["frames_per_s"], d["ms_per_step"], d["e2e"]["frames_per_s"]), d["kernel_ms_per_step_rank0"])
     except Exception as e: print(f, "failed", e)
 PY
+python - <<PY
+import json,glob
+for f in sorted(glob.glob("gpurun_out/${tag}_n*_peer_*.json")):
+    try:
+        d=json.load(open(f)); print(f); [print("   ", x) for x in d["kernel_ms_per_step_by_rank"]]
+    except Exception as e: print(f, "failed", e)
+PY

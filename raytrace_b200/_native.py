@@ -98,6 +98,7 @@ SYMBOLS = {
     "vxrt_comm_gather_output": (C.c_int, [_H, C.c_int]),
     "vxrt_comm_broadcast_edits": (C.c_int, [_H, C.c_void_p, C.c_size_t, C.c_int]),
     "vxrt_peer_export": (C.c_int, [_H, C.c_void_p, C.c_size_t]),
+    "vxrt_peer_barrier": (C.c_int, [_H]),
     "vxrt_peer_attach": (C.c_int, [_H, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_int]),
 }
 COMM_ID_BYTES = 128

@@ -6,6 +6,7 @@
 #include <math.h>
 #include <stdio.h>
 #include <string.h>
+#include <stdlib.h>
 #include <new>
 
 namespace {
@@ -561,9 +562,28 @@ int vxrt_render_frame(VxrtHandle* h) {
     if (h->peer_on && (prc = vxrt_peer_begin_frame(h, h->out_idx))) return prc;
     CU(cudaMemsetAsync(h->d_counters, 0, 8 * sizeof(unsigned long long), h->stream));
     CU(cudaEventRecord(h->ev[0], h->stream));
-    CU(vxrt_launch_trace(P, h->stream));
+    if (!h->peer_on) {
+        CU(vxrt_launch_trace(P, h->stream));
+    } else {
+        // peer.cu: the rows a neighbour's denoise needs are traced first and stored into its images while this
+        // band's interior is still being traced
+        int32_t iv[2 * VXRT_PEER_MAX_LINKS];
+        // measured at N=2 (profiles/r1_m): splitting the trace pass into boundary + interior launches costs more in partial
+        // waves than the earlier push wins, so the whole band is traced first; the split stays behind a switch
+        static const bool boundary_first = getenv("VXRT_PEER_BOUNDARY_FIRST") != nullptr;
+        const int n = boundary_first ? vxrt_peer_boundary_rows(h, iv) : 0;
+        for (int i = 0; i < n; i++) { P.row0 = iv[2 * i]; P.row1 = iv[2 * i + 1]; CU(vxrt_launch_trace(P, h->stream)); }
+        if (n && (prc = vxrt_peer_push_halo(h))) return prc;
+        int at = h->row0;
+        for (int i = 0; i <= n; i++) {
+            const int gap_end = i < n ? iv[2 * i] : h->row1;
+            if (gap_end > at) { P.row0 = at; P.row1 = gap_end; CU(vxrt_launch_trace(P, h->stream)); }
+            if (i < n) at = iv[2 * i + 1];
+        }
+        if (!n && (prc = vxrt_peer_push_halo(h))) return prc;
+    }
     CU(cudaEventRecord(h->ev[1], h->stream));
-    if (h->peer_on && (prc = vxrt_peer_exchange_halo(h))) return prc;       // rows the neighbours' denoise needs (peer.cu)
+    if (h->peer_on && (prc = vxrt_peer_wait_halo(h))) return prc;
     if (h->d_lighting_raw)
         CU(cudaMemcpyAsync(h->d_lighting_raw, h->d_lighting, pixels(h) * 8, cudaMemcpyDeviceToDevice, h->stream));
     if (h->d_accum) h->frames_accumulated++;
@@ -584,10 +604,13 @@ int vxrt_render_frame(VxrtHandle* h) {
         CU(cudaStreamWaitEvent(h->stream, h->ev_copy_done[h->out_idx], 0));
         h->copy_pending[h->out_idx] = false;
     }
-    if (h->cfg.flags & VXRT_FLAG_FINALIZE)
+    if (h->cfg.flags & VXRT_FLAG_FINALIZE) {
+        VxrtPeerTail tail;
+        if (h->peer_on) tail = vxrt_peer_finalize_tail(h);
         CU(vxrt_launch_finalize(h->d_albedo, h->d_emission, h->d_fog, h->d_lighting, h->d_depth, h->d_noise,
                                 h->peer_on ? vxrt_peer_output(h, h->out_idx) : h->d_output,       // peer mode: straight into the root's image
-                                h->cfg.width, h->cfg.height, h->row0, h->row1, h->stream));
+                                h->cfg.width, h->cfg.height, h->row0, h->row1, h->stream, h->peer_on ? &tail : nullptr));
+    }
     if (h->peer_on && (prc = vxrt_peer_end_frame(h))) return prc;
     CU(cudaEventRecord(h->ev[3], h->stream));
     h->rendered = true;

@@ -22,6 +22,9 @@
 #include "vxrt_internal.h"
 #include <string.h>
 #include <unistd.h>
+#include <algorithm>
+#include <utility>
+#include "peer_dev.cuh"
 
 namespace {
 
@@ -33,8 +36,8 @@ namespace {
 
 // flag words (uint32 frame counters) in every handle's d_peer_flags
 enum { F_ARRIVED = 0, F_CONSUMED = VXRT_PEER_MAX_RANKS, F_BAND_DONE = 2 * VXRT_PEER_MAX_RANKS, F_RELEASED = 3 * VXRT_PEER_MAX_RANKS,
-       F_ERROR = 3 * VXRT_PEER_MAX_RANKS + 1, F_PUSH_TICKET = 3 * VXRT_PEER_MAX_RANKS + 2,
-       F_COUNT = 3 * VXRT_PEER_MAX_RANKS + 2 + VXRT_PEER_MAX_LINKS };
+       F_ERROR = 3 * VXRT_PEER_MAX_RANKS + 1, F_FIN_TICKET = 3 * VXRT_PEER_MAX_RANKS + 2, F_BARRIER = 4 * VXRT_PEER_MAX_RANKS,
+       F_PUSH_TICKET = 5 * VXRT_PEER_MAX_RANKS, F_COUNT = 5 * VXRT_PEER_MAX_RANKS + VXRT_PEER_MAX_LINKS };
 
 struct PeerBlob {                        // what vxrt_peer_export writes; VXRT_PEER_BLOB_BYTES on the wire
     uint32_t magic, version;
@@ -47,34 +50,23 @@ struct PeerBlob {                        // what vxrt_peer_export writes; VXRT_P
 static_assert(sizeof(PeerBlob) <= VXRT_PEER_BLOB_BYTES, "PeerBlob must fit VXRT_PEER_BLOB_BYTES");
 constexpr uint32_t kMagic = 0x56585250u;   // "VXRP"
 
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
-    uint32_t v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
-}
-
 struct SyncList { const uint32_t* wait[VXRT_PEER_MAX_LINKS]; uint32_t* post[VXRT_PEER_MAX_LINKS]; int n_wait, n_post; };
-
-// spin until every wait word >= value; ~4 s bound, then flag the error word and carry on (never hang the GPU)
-__device__ bool spin_until(const uint32_t* p, uint32_t value, uint32_t* err) {
-    const long long t0 = clock64();
-    while ((int32_t)(ld_acquire_sys(p) - value) < 0) {
-        if (clock64() - t0 > 8000000000LL) { atomicExch(err, value ? value : 1u); return false; }
-        __nanosleep(64);
-    }
-    return true;
-}
 
 // one warp: lane i waits on wait[i]; then lane i posts to post[i]
 __global__ void k_peer_sync(SyncList s, uint32_t wait_value, uint32_t post_value, uint32_t* err) {
     const int i = threadIdx.x;
-    if (i < s.n_wait) spin_until(s.wait[i], wait_value, err);
+    if (i < s.n_wait) vx_spin_until(s.wait[i], wait_value, err);
     __syncwarp();
     __threadfence_system();
-    if (i < s.n_post) st_release_sys(s.post[i], post_value);
+    if (i < s.n_post) vx_st_release_sys(s.post[i], post_value);
+}
+
+// post first, then wait: every rank announces itself before looking at the others
+__global__ void k_peer_barrier(SyncList s, uint32_t value, uint32_t* err) {
+    const int i = threadIdx.x;
+    __threadfence_system();
+    if (i < s.n_post) vx_st_release_sys(s.post[i], value);
+    if (i < s.n_wait) vx_spin_until(s.wait[i], value, err);
 }
 
 struct PushLink {                        // rows [r0,r1) of my band go to one neighbour
@@ -105,21 +97,20 @@ __device__ void copy_range(uint8_t* dst, const uint8_t* src, size_t n, size_t ti
 __global__ void __launch_bounds__(256) k_halo_push(PushParams p) {
     const PushLink& L = p.link[blockIdx.y];
     __shared__ bool last;
-    if (threadIdx.x == 0) spin_until(L.consumed, p.frame - 1, p.err);
+    if (threadIdx.x == 0) vx_spin_until(L.consumed, p.frame - 1, p.err);
     __syncthreads();
     const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nt = (size_t)gridDim.x * blockDim.x;
     const size_t a = (size_t)L.r0 * p.width, n = (size_t)(L.r1 - L.r0) * p.width;
     copy_range(reinterpret_cast<uint8_t*>(L.lighting + a), reinterpret_cast<const uint8_t*>(p.lighting + a), n * 8, tid, nt);
     copy_range(reinterpret_cast<uint8_t*>(L.depth + a), reinterpret_cast<const uint8_t*>(p.depth + a), n * 2, tid, nt);
     copy_range(L.normal + a, p.normal + a, n, tid, nt);
-    __threadfence_system();
-    __syncthreads();
-    if (threadIdx.x == 0) last = atomicAdd(p.ticket + blockIdx.y, 1u) == gridDim.x - 1;
+    __syncthreads();                                       // the CTA's stores happen-before thread 0's fence
+    if (threadIdx.x == 0) { __threadfence_system(); last = atomicAdd(p.ticket + blockIdx.y, 1u) == gridDim.x - 1; }
     __syncthreads();
     if (last && threadIdx.x == 0) {
         p.ticket[blockIdx.y] = 0;
         __threadfence_system();
-        st_release_sys(L.arrived, p.frame);
+        vx_st_release_sys(L.arrived, p.frame);
     }
 }
 
@@ -170,8 +161,24 @@ int vxrt_peer_begin_frame(VxrtHandle* h, int out_idx) {
     return VXRT_OK;
 }
 
-// after the trace pass: push my rows into the neighbours' images, then wait for theirs
-int vxrt_peer_exchange_halo(VxrtHandle* h) {
+// Rows of this band some neighbour's denoise needs, merged into disjoint ascending intervals (a0,b0,a1,b1,...).
+// vxrt_render_frame traces these first and pushes them, then traces the interior, so a neighbour's halo is normally
+// on its way long before that neighbour finishes its own trace pass.
+int vxrt_peer_boundary_rows(VxrtHandle* h, int32_t* iv /* 2 * VXRT_PEER_MAX_LINKS */) {
+    if (!(h->cfg.flags & VXRT_FLAG_DENOISE)) return 0;
+    std::vector<std::pair<int, int>> v;
+    for (const VxrtPeerLink& d : h->peer_dst) v.push_back({d.r0, d.r1});
+    std::sort(v.begin(), v.end());
+    int n = 0;
+    for (const auto& p : v) {
+        if (n && p.first <= iv[2 * n - 1]) { if (p.second > iv[2 * n - 1]) iv[2 * n - 1] = p.second; }
+        else { iv[2 * n] = p.first; iv[2 * n + 1] = p.second; n++; }
+    }
+    return n;
+}
+
+// after the boundary rows are traced: store them into the neighbours' images
+int vxrt_peer_push_halo(VxrtHandle* h) {
     if (!(h->cfg.flags & VXRT_FLAG_DENOISE)) return VXRT_OK;
     if (!h->peer_dst.empty()) {
         PushParams p; memset(&p, 0, sizeof p);
@@ -193,6 +200,12 @@ int vxrt_peer_exchange_halo(VxrtHandle* h) {
         k_halo_push<<<dim3(ctas, p.n), 256, 0, h->stream>>>(p);
         CU(cudaGetLastError());
     }
+    return VXRT_OK;
+}
+
+// before the first denoise pass: the neighbours' rows must have landed
+int vxrt_peer_wait_halo(VxrtHandle* h) {
+    if (!(h->cfg.flags & VXRT_FLAG_DENOISE)) return VXRT_OK;
     if (!h->peer_src.empty()) {
         SyncList s; memset(&s, 0, sizeof s);
         for (const VxrtPeerLink& l : h->peer_src) s.wait[s.n_wait++] = h->d_peer_flags + F_ARRIVED + l.rank;
@@ -202,15 +215,26 @@ int vxrt_peer_exchange_halo(VxrtHandle* h) {
     return VXRT_OK;
 }
 
-// after the last denoise pass: the halo rows are free again; a non-root also waits for the root's output buffer
-int vxrt_peer_after_denoise(VxrtHandle* h) {
-    SyncList s; memset(&s, 0, sizeof s);
+// The frame's last signals ride in k_finalize (post.cu): its prologue waits for the root's RELEASED word (non-root),
+// its last CTA posts CONSUMED to the halo sources and BAND_DONE to the root.  Returns the tail to hand to the launch.
+VxrtPeerTail vxrt_peer_finalize_tail(VxrtHandle* h) {
+    VxrtPeerTail t; memset(&t, 0, sizeof t);
+    t.value = h->peer_frame; t.err = h->d_peer_flags + F_ERROR; t.ticket = h->d_peer_flags + F_FIN_TICKET;
     if (h->cfg.flags & VXRT_FLAG_DENOISE)
-        for (const VxrtPeerLink& l : h->peer_src) s.post[s.n_post++] = h->peer_flags[l.rank] + F_CONSUMED + h->rank;
-    const bool wait_root = h->rank != h->peer_root && (h->cfg.flags & VXRT_FLAG_FINALIZE);
-    if (wait_root) s.wait[s.n_wait++] = h->d_peer_flags + F_RELEASED;
-    if (!s.n_post && !s.n_wait) return VXRT_OK;
-    k_peer_sync<<<1, 32, 0, h->stream>>>(s, h->peer_frame, h->peer_frame, h->d_peer_flags + F_ERROR);
+        for (const VxrtPeerLink& l : h->peer_src) t.post[t.n_post++] = h->peer_flags[l.rank] + F_CONSUMED + h->rank;
+    if (h->rank != h->peer_root) {
+        t.wait = h->d_peer_flags + F_RELEASED;
+        t.post[t.n_post++] = h->peer_flags[h->peer_root] + F_BAND_DONE + h->rank;
+    }
+    return t;
+}
+
+// without a finalize pass the CONSUMED words still have to be posted after the last denoise pass
+int vxrt_peer_after_denoise(VxrtHandle* h) {
+    if ((h->cfg.flags & VXRT_FLAG_FINALIZE) || !(h->cfg.flags & VXRT_FLAG_DENOISE) || h->peer_src.empty()) return VXRT_OK;
+    SyncList s; memset(&s, 0, sizeof s);
+    for (const VxrtPeerLink& l : h->peer_src) s.post[s.n_post++] = h->peer_flags[l.rank] + F_CONSUMED + h->rank;
+    k_peer_sync<<<1, 32, 0, h->stream>>>(s, 0, h->peer_frame, h->d_peer_flags + F_ERROR);
     CU(cudaGetLastError());
     return VXRT_OK;
 }
@@ -220,13 +244,12 @@ uchar4* vxrt_peer_output(VxrtHandle* h, int out_idx) {
     return h->rank == h->peer_root ? h->d_out_buf[out_idx] : (uchar4*)h->peer_root_out[out_idx];
 }
 
-// after k_finalize: a non-root publishes its band; the root waits for every band
+// after k_finalize on the root: wait for every band
 int vxrt_peer_end_frame(VxrtHandle* h) {
-    if (!(h->cfg.flags & VXRT_FLAG_FINALIZE)) return VXRT_OK;
+    if (!(h->cfg.flags & VXRT_FLAG_FINALIZE) || h->rank != h->peer_root || h->nranks == 1) return VXRT_OK;
     SyncList s; memset(&s, 0, sizeof s);
-    if (h->rank != h->peer_root) s.post[s.n_post++] = h->peer_flags[h->peer_root] + F_BAND_DONE + h->rank;
-    else for (int r = 0; r < h->nranks; r++) if (r != h->rank) s.wait[s.n_wait++] = h->d_peer_flags + F_BAND_DONE + r;
-    k_peer_sync<<<1, 32, 0, h->stream>>>(s, h->peer_frame, h->peer_frame, h->d_peer_flags + F_ERROR);
+    for (int r = 0; r < h->nranks; r++) if (r != h->rank) s.wait[s.n_wait++] = h->d_peer_flags + F_BAND_DONE + r;
+    k_peer_sync<<<1, 32, 0, h->stream>>>(s, h->peer_frame, 0, h->d_peer_flags + F_ERROR);
     CU(cudaGetLastError());
     return VXRT_OK;
 }
@@ -260,6 +283,23 @@ int vxrt_peer_export(VxrtHandle* h, void* blob, size_t nbytes) {
     }
     memset(blob, 0, VXRT_PEER_BLOB_BYTES);
     memcpy(blob, &b, sizeof b);
+    return VXRT_OK;
+}
+
+// device-side barrier over all ranks on the handle's stream (benchmarks: align the ranks before a timed frame)
+int vxrt_peer_barrier(VxrtHandle* h) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (!h->peer_on) { h->err = "vxrt_peer_barrier: vxrt_peer_attach not called"; return VXRT_ERR_STATE; }
+    CU(cudaSetDevice(h->cfg.device));
+    h->peer_barriers++;
+    SyncList s; memset(&s, 0, sizeof s);
+    for (int r = 0; r < h->nranks; r++) {
+        if (r == h->rank) continue;
+        s.post[s.n_post++] = h->peer_flags[r] + F_BARRIER + h->rank;
+        s.wait[s.n_wait++] = h->d_peer_flags + F_BARRIER + r;
+    }
+    k_peer_barrier<<<1, 32, 0, h->stream>>>(s, h->peer_barriers, h->d_peer_flags + F_ERROR);
+    CU(cudaGetLastError());
     return VXRT_OK;
 }
 
@@ -298,7 +338,7 @@ int vxrt_peer_attach(VxrtHandle* h, const void* blobs, size_t nbytes, int rank, 
         const int d0 = h->row0 > plan[0] ? h->row0 : plan[0], d1 = h->row1 < plan[1] ? h->row1 : plan[1];
         const int s0 = all[r].row0 > h->plan[0] ? all[r].row0 : h->plan[0], s1 = all[r].row1 < h->plan[1] ? all[r].row1 : h->plan[1];
         const bool dst = (h->cfg.flags & VXRT_FLAG_DENOISE) && d0 < d1, src = (h->cfg.flags & VXRT_FLAG_DENOISE) && s0 < s1;
-        const bool need_flags = dst || src || r == root || rank == root;
+        const bool need_flags = true;                      // vxrt_peer_barrier posts to every rank
         if (need_flags) {
             void* f = nullptr;
             if ((rc = open_peer(h, all[r], 5, &f))) return rc;

@@ -1,6 +1,8 @@
 // post.cu — k_denoise (shaders/glsl/bilateral_denoise.comp) and k_finalize (shaders/glsl/finalize.comp).
 // Same explicit-rounding rule as trace.cu so the 16-bit / 8-bit images match the oracle bit for bit.
 #include "vxrt_internal.h"
+#include "peer_dev.cuh"
+#include <string.h>
 
 namespace {
 
@@ -214,12 +216,25 @@ __device__ __forceinline__ float filmic_curve(float x) {
 // finalize.comp:33-64.  Colour work under the tolerance contract (<= 1/255 per channel): UNORM decodes are
 // reciprocal multiplies folded into the constants, FMA contraction allowed (the IEEE-division form spent ~480
 // instructions per pixel and was issue-bound; this one is bound by its 30 B/pixel of traffic).
+template <bool PEER>
 __global__ void __launch_bounds__(256) k_finalize(const uchar4* __restrict__ albedo, const uchar4* __restrict__ emission,
                                                   const uchar4* __restrict__ fog, const ushort4* __restrict__ lighting,
                                                   const uint16_t* __restrict__ depth, const uint8_t* __restrict__ noise,
-                                                  uchar4* __restrict__ out, int width, int height, int row0, int row1) {
-    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = row0 + blockIdx.y * 8 + (threadIdx.x >> 5);
-    if (x >= width || y >= row1) return;
+                                                  uchar4* __restrict__ out, int width, int height, int row0, int row1,
+                                                  const __grid_constant__ VxrtPeerTail tail) {
+    // peer mode (peer.cu): `out` is the ROOT's image in peer memory; do not store into it before the root released it
+    if (PEER && tail.wait) {
+        if (threadIdx.x == 0) vx_spin_until(tail.wait, tail.value, tail.err);
+        __syncthreads();
+    }
+    // grid-stride over 32x8-pixel tiles: a few CTAs per SM, so the peer-mode tail costs one fence + one ticket per
+    // CTA, not per tile
+    // (PEER only; the single-GPU form is one tile per CTA of a 2-D grid)
+    const int tiles_x = (width + 31) / 32, ntiles = tiles_x * ((row1 - row0 + 7) / 8);
+    for (int tile = PEER ? blockIdx.x : 0; tile < (PEER ? ntiles : 1); tile += gridDim.x) {
+    const int ty = PEER ? tile / tiles_x : blockIdx.y, tx = PEER ? tile - ty * tiles_x : blockIdx.x;
+    const int x = tx * 32 + (threadIdx.x & 31), y = row0 + ty * 8 + (threadIdx.x >> 5);
+    if (x >= width || y >= row1) continue;
     const size_t pi = (size_t)y * width + x;
     const uchar4 a = __ldg(albedo + pi), e = __ldg(emission + pi), f = __ldg(fog + pi);
     const ushort4 l = __ldg(lighting + pi);
@@ -238,6 +253,18 @@ __global__ void __launch_bounds__(256) k_finalize(const uchar4* __restrict__ alb
         o[k] = __float2uint_rn(__saturatef(v) * 255.0f);
     }
     out[(size_t)(height - y - 1) * width + x] = make_uchar4((unsigned char)o[0], (unsigned char)o[1], (unsigned char)o[2], 255);   // :60-63
+    }
+    if (PEER && tail.n_post) {                             // the last CTA to finish publishes the frame number
+        __shared__ bool last;
+        __syncthreads();                                   // the CTA's stores happen-before thread 0's fence
+        if (threadIdx.x == 0) { __threadfence_system(); last = atomicAdd(tail.ticket, 1u) == gridDim.x - 1; }
+        __syncthreads();
+        if (last && threadIdx.x < tail.n_post) {
+            if (threadIdx.x == 0) *tail.ticket = 0;
+            __threadfence_system();
+            vx_st_release_sys(tail.post[threadIdx.x], tail.value);
+        }
+    }
 }
 
 // Per-row work counters of the last frame for the load-balanced band plan (vxrt_plan_bands_weighted): march
@@ -283,9 +310,13 @@ cudaError_t vxrt_launch_denoise(const ushort4* src, ushort4* dst, const uint16_t
 
 cudaError_t vxrt_launch_finalize(const uchar4* albedo, const uchar4* emission, const uchar4* fog, const ushort4* lighting,
                                  const uint16_t* depth, const uint8_t* noise, uchar4* out, int width, int height,
-                                 int row0, int row1, cudaStream_t s) {
+                                 int row0, int row1, cudaStream_t s, const VxrtPeerTail* tail) {
     if (row1 <= row0) return cudaSuccess;
-    dim3 grid((width + 31) / 32, (row1 - row0 + 7) / 8);
-    k_finalize<<<grid, 256, 0, s>>>(albedo, emission, fog, lighting, depth, noise, out, width, height, row0, row1);
+    const int ntiles = ((width + 31) / 32) * ((row1 - row0 + 7) / 8);
+    VxrtPeerTail none; memset(&none, 0, sizeof none);
+    if (tail)       // peer tail: one fence + ticket per CTA, so keep the CTA count low
+        k_finalize<true><<<ntiles > 148 * 8 ? 148 * 8 : ntiles, 256, 0, s>>>(albedo, emission, fog, lighting, depth, noise, out, width, height, row0, row1, *tail);
+    else
+        k_finalize<false><<<dim3((width + 31) / 32, (row1 - row0 + 7) / 8), 256, 0, s>>>(albedo, emission, fog, lighting, depth, noise, out, width, height, row0, row1, none);
     return cudaGetLastError();
 }

@@ -44,6 +44,10 @@ struct TraceParams {
 // one halo link of the peer-memory frame (peer.cu): rows [r0,r1) go to / come from `rank`
 struct VxrtPeerLink { int rank, r0, r1; void *lighting, *depth, *normal; };
 
+// cross-GPU signals carried by k_finalize in peer mode (peer.cu): wait word checked by every CTA before it stores
+// into the root's image, flag words posted by the last CTA after its stores are fenced
+struct VxrtPeerTail { const uint32_t* wait; uint32_t* post[VXRT_PEER_MAX_LINKS + 1]; int n_post; uint32_t value; uint32_t* ticket; uint32_t* err; };
+
 struct VxrtHandle {
     VxrtConfig cfg;
     int row0, row1;                      // rendered G-buffer rows
@@ -71,7 +75,7 @@ struct VxrtHandle {
     // multi-GPU (comm.cu)
     void* comm; int rank, nranks; std::vector<int32_t> bands;   // bands[2r], bands[2r+1] = rows of rank r
     // multi-GPU over peer memory (peer.cu)
-    bool peer_on = false; int peer_root = 0; uint32_t peer_frame = 0;
+    bool peer_on = false; int peer_root = 0; uint32_t peer_frame = 0, peer_barriers = 0;
     uint32_t* d_peer_flags = nullptr;                            // this handle's flag words (exported)
     std::vector<uint32_t*> peer_flags;                           // every rank's flag words as seen from this device
     std::vector<VxrtPeerLink> peer_dst, peer_src;
@@ -82,8 +86,11 @@ struct VxrtHandle {
 void vxrt_comm_release(VxrtHandle* h);
 void vxrt_peer_release(VxrtHandle* h);
 int vxrt_peer_begin_frame(VxrtHandle* h, int out_idx);
-int vxrt_peer_exchange_halo(VxrtHandle* h);
+int vxrt_peer_boundary_rows(VxrtHandle* h, int32_t* iv);
+int vxrt_peer_push_halo(VxrtHandle* h);
+int vxrt_peer_wait_halo(VxrtHandle* h);
 int vxrt_peer_after_denoise(VxrtHandle* h);
+VxrtPeerTail vxrt_peer_finalize_tail(VxrtHandle* h);
 uchar4* vxrt_peer_output(VxrtHandle* h, int out_idx);
 int vxrt_peer_end_frame(VxrtHandle* h);
 int vxrt_peer_error_word(VxrtHandle* h, uint32_t* out);
@@ -95,7 +102,7 @@ cudaError_t vxrt_launch_denoise(const ushort4* src, ushort4* dst, const uint16_t
                                 int width, int height, int size, int swap, int row0, int row1, cudaStream_t s);
 cudaError_t vxrt_launch_finalize(const uchar4* albedo, const uchar4* emission, const uchar4* fog, const ushort4* lighting,
                                  const uint16_t* depth, const uint8_t* noise, uchar4* out, int width, int height,
-                                 int row0, int row1, cudaStream_t s);
+                                 int row0, int row1, cudaStream_t s, const VxrtPeerTail* tail = nullptr);
 cudaError_t vxrt_launch_row_cost(const uint32_t* steps, const uint8_t* rays, const uint8_t* normal, int width, int height,
                                  float* out /* 3 per row: steps, rays, filtered pixels */, cudaStream_t s);
 cudaError_t vxrt_launch_build_minefield(uint32_t* materials, uint8_t* minefield, int nx, int ny, int nz,
