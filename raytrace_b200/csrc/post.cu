@@ -46,6 +46,10 @@ constexpr int DN_TX = 128;                     // pixels per CTA row
 constexpr int DN_TY = VXRT_DN_TY;              // thread rows per CTA
 constexpr int DN_G = 4;                        // vertically adjacent outputs per thread
 // decimated rows a thread walks per tile: dilations 1,2,4 / dilations 8,16 (wider x halo -> shorter tile)
+#ifndef VXRT_DN_UNROLL
+#define VXRT_DN_UNROLL 2
+#endif
+constexpr int DN_UNROLL = VXRT_DN_UNROLL;      // staging loop unroll (global loads in flight per thread)
 #ifndef VXRT_DN_L0
 #define VXRT_DN_L0 8
 #endif
@@ -100,6 +104,7 @@ __global__ void __launch_bounds__(DN_TX * DN_TY) k_denoise(const ushort4* __rest
         }
     }
     // stage: texel (tx, ty) <- image (clamp(bx + tx - 3S), clamp(ybase + (ty - 3) * S))   (sampleAt, :14-21)
+#pragma unroll DN_UNROLL
     for (int e = tid; e < T::N; e += DN_TX * DN_TY) {
         const int ty = e / T::W, tx = e - ty * T::W;
         const int gx = min(max(bx + tx - 3 * S, 0), width - 1), gy = min(max(ybase + (ty - 3) * S, 0), height - 1);
