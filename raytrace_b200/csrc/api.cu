@@ -289,6 +289,8 @@ int vxrt_create(const VxrtConfig* cfg, VxrtHandle** out) {
     h->h_noise.assign((size_t)VXRT_NOISE_SIZE * VXRT_NOISE_SIZE * 4, 0);
 
     auto init = [&]() -> int {
+        // load every kernel now: a lazy load at first launch cannot complete while a peer-mode kernel spins on a flag
+        CU(vxrt_preload_trace()); CU(vxrt_preload_trace_fast()); CU(vxrt_preload_post()); CU(vxrt_preload_world()); CU(vxrt_preload_peer());
         CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
         for (int i = 0; i < 5; i++) CU(cudaEventCreate(&h->ev[i]));
         CU(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));

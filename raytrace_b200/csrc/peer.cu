@@ -135,6 +135,11 @@ int open_peer(VxrtHandle* h, const PeerBlob& b, int which, void** out) {
 
 }  // namespace
 
+// CUDA loads a kernel's code at its first launch, and that load cannot complete while another kernel is resident
+// and spinning on a flag (peer.cu).  Every kernel of this file is therefore loaded when a handle is created.
+#define VXRT_PRELOAD(k) do { cudaFuncAttributes a_; cudaError_t e_ = cudaFuncGetAttributes(&a_, k); if (e_ != cudaSuccess) return e_; } while (0)
+cudaError_t vxrt_preload_peer() { VXRT_PRELOAD(k_peer_sync); VXRT_PRELOAD(k_peer_barrier); VXRT_PRELOAD(k_halo_push); return cudaSuccess; }
+
 void vxrt_peer_release(VxrtHandle* h) {
     for (void* p : h->peer_ipc_opened) cudaIpcCloseMemHandle(p);
     h->peer_ipc_opened.clear();

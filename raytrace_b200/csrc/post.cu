@@ -294,6 +294,19 @@ __global__ void __launch_bounds__(256) k_row_cost(const uint32_t* __restrict__ s
 
 }  // namespace
 
+
+// CUDA loads a kernel's code at its first launch, and that load cannot complete while another kernel is resident
+// and spinning on a flag (peer.cu).  Every kernel of this file is therefore loaded when a handle is created.
+#define VXRT_PRELOAD(k) do { cudaFuncAttributes a_; cudaError_t e_ = cudaFuncGetAttributes(&a_, k); if (e_ != cudaSuccess) return e_; } while (0)
+template <int S, int L> cudaError_t preload_denoise() { VXRT_PRELOAD((k_denoise<S, L, false>)); VXRT_PRELOAD((k_denoise<S, L, true>)); return cudaSuccess; }
+cudaError_t vxrt_preload_post() {
+    cudaError_t e;
+    if ((e = preload_denoise<1, VXRT_DN_L0>()) || (e = preload_denoise<2, VXRT_DN_L0>()) || (e = preload_denoise<4, VXRT_DN_L0>()) ||
+        (e = preload_denoise<8, VXRT_DN_L1>()) || (e = preload_denoise<16, VXRT_DN_L1>())) return e;
+    VXRT_PRELOAD(k_finalize<false>); VXRT_PRELOAD(k_finalize<true>); VXRT_PRELOAD(k_row_cost);
+    return cudaSuccess;
+}
+
 cudaError_t vxrt_launch_row_cost(const uint32_t* steps, const uint8_t* rays, const uint8_t* normal, int width, int height,
                                  float* out, cudaStream_t s) {
     k_row_cost<<<height, 256, 0, s>>>(steps, rays, normal, width, out);

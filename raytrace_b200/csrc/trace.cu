@@ -200,6 +200,10 @@ __global__ void __launch_bounds__(128) k_trace_general(const __grid_constant__ T
 
 }  // namespace
 
+// see peer.cu: every kernel is loaded when a handle is created (a lazy load cannot complete under a spinning kernel)
+#define VXRT_PRELOAD(k) do { cudaFuncAttributes a_; cudaError_t e_ = cudaFuncGetAttributes(&a_, k); if (e_ != cudaSuccess) return e_; } while (0)
+cudaError_t vxrt_preload_trace() { VXRT_PRELOAD(k_trace_general); return cudaSuccess; }
+
 cudaError_t vxrt_launch_trace(const TraceParams& p, cudaStream_t s) {
     const int rows = p.row1 - p.row0;
     if (rows <= 0) return cudaSuccess;

@@ -95,6 +95,10 @@ uchar4* vxrt_peer_output(VxrtHandle* h, int out_idx);
 int vxrt_peer_end_frame(VxrtHandle* h);
 int vxrt_peer_error_word(VxrtHandle* h, uint32_t* out);
 
+// module preload (cudaFuncGetAttributes on every kernel of a file)
+cudaError_t vxrt_preload_trace(); cudaError_t vxrt_preload_trace_fast(); cudaError_t vxrt_preload_post();
+cudaError_t vxrt_preload_world(); cudaError_t vxrt_preload_peer();
+
 // launchers (each returns the cudaGetLastError() of its launch)
 cudaError_t vxrt_launch_trace(const TraceParams& p, cudaStream_t s);        // dispatches on p.fast
 cudaError_t vxrt_launch_trace_fast(const TraceParams& p, cudaStream_t s);

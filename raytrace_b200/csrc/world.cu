@@ -176,6 +176,10 @@ __global__ void __launch_bounds__(256) k_generate(uint32_t* __restrict__ materia
 
 }  // namespace
 
+// see peer.cu: every kernel is loaded when a handle is created (a lazy load cannot complete under a spinning kernel)
+#define VXRT_PRELOAD(k) do { cudaFuncAttributes a_; cudaError_t e_ = cudaFuncGetAttributes(&a_, k); if (e_ != cudaSuccess) return e_; } while (0)
+cudaError_t vxrt_preload_world() { VXRT_PRELOAD(k_build_minefield); VXRT_PRELOAD(k_apply_edits); VXRT_PRELOAD(k_generate); return cudaSuccess; }
+
 cudaError_t vxrt_launch_build_minefield(uint32_t* materials, uint8_t* minefield, int nx, int ny, int nz,
                                         const uint32_t* dirty, cudaStream_t s) {
     const int chunks = (nx >> 6) * (ny >> 6) * (nz >> 6);
