@@ -44,6 +44,9 @@ constexpr int DN_TX = 128;                     // pixels per CTA row
 #define VXRT_DN_TY 2
 #endif
 constexpr int DN_TY = VXRT_DN_TY;              // thread rows per CTA
+#ifndef VXRT_DN_MINB
+#define VXRT_DN_MINB 5                         // 48 registers: 5 CTAs/SM where shared memory allows (S <= 8)
+#endif
 constexpr int DN_G = 4;                        // vertically adjacent outputs per thread
 // decimated rows a thread walks per tile: dilations 1,2,4 / dilations 8,16 (wider x halo -> shorter tile)
 #ifndef VXRT_DN_UNROLL
@@ -70,7 +73,7 @@ __host__ __device__ constexpr float dn_weight(int ax, int ay) {
 }
 
 template <int S, int L, bool SWAP>
-__global__ void __launch_bounds__(DN_TX * DN_TY) k_denoise(const ushort4* __restrict__ src, ushort4* __restrict__ dst,
+__global__ void __launch_bounds__(DN_TX * DN_TY, VXRT_DN_MINB) k_denoise(const ushort4* __restrict__ src, ushort4* __restrict__ dst,
                                                    const uint16_t* __restrict__ depth, const uint8_t* __restrict__ normal,
                                                    int width, int height, int row0, int row1, int groups) {
     using T = DnTile<S, L>;
