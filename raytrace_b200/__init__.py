@@ -6,7 +6,8 @@ from .render import (Camera, Material, MATERIALS, Pipeline, Renderer, VxrtError,
                      compute_triple_euler_vector, fill_uniform_data, load_materials_csv, plan_bands, plan_bands_weighted, plan_passes)
 from .game import Game
 from .world import ChunkStorage, PackedChunkData
+from .terrain_upload import TerrainUploadManager
 
 __all__ = ["Camera", "Material", "MATERIALS", "Pipeline", "Renderer", "VxrtError", "constants", "create_instance",
            "compute_triple_euler_vector", "fill_uniform_data", "load_materials_csv", "plan_bands", "plan_bands_weighted", "plan_passes", "Game", "ChunkStorage",
-           "PackedChunkData"]
+           "PackedChunkData", "TerrainUploadManager"]
