@@ -206,6 +206,15 @@ int  vxrt_comm_gather_output(VxrtHandle* h, int root);
 int  vxrt_comm_broadcast_edits(VxrtHandle* h, const VxrtEdit* edits, size_t n, int root);
 
 
+/* ---- chunk files (host only; no device needed) --------------------------------------------------------
+ * The reference's on-disk chunk format (src/world/chunk_storage.rs:37-68): file name = three {:016X} fields of the
+ * signed chunk coordinates; contents = LZ4 frame of materials (u32 LE x 64^3) followed by minefield (u8 x 64^3).
+ * vxrt_chunk_decode output feeds vxrt_upload_chunk directly. */
+int    vxrt_chunk_file_name(int64_t cx, int64_t cy, int64_t cz, char* out /* >= 49 bytes */, size_t nbytes);
+size_t vxrt_chunk_encode_bound(void);
+int    vxrt_chunk_encode(const uint32_t* materials, const uint8_t* minefield, void* out, size_t cap, size_t* nbytes);
+int    vxrt_chunk_decode(const void* file, size_t nbytes, uint32_t* materials, uint8_t* minefield);
+
 /* ---- multi-GPU frame over NVLink peer memory (no NCCL on the per-frame path; peer.cu) ---------------------
  * After vxrt_peer_attach a band traces only its own rows: the rows of lighting/depth/normal a neighbour's
  * denoise needs are stored straight into that neighbour's images, the final RGBA8 band is stored by the

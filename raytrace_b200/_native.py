@@ -97,6 +97,10 @@ SYMBOLS = {
     "vxrt_comm_init": (C.c_int, [_H, C.c_void_p, C.c_size_t, C.c_int, C.c_int]),
     "vxrt_comm_gather_output": (C.c_int, [_H, C.c_int]),
     "vxrt_comm_broadcast_edits": (C.c_int, [_H, C.c_void_p, C.c_size_t, C.c_int]),
+    "vxrt_chunk_file_name": (C.c_int, [C.c_int64, C.c_int64, C.c_int64, C.c_char_p, C.c_size_t]),
+    "vxrt_chunk_encode_bound": (C.c_size_t, []),
+    "vxrt_chunk_encode": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "vxrt_chunk_decode": (C.c_int, [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]),
     "vxrt_peer_export": (C.c_int, [_H, C.c_void_p, C.c_size_t]),
     "vxrt_peer_barrier": (C.c_int, [_H]),
     "vxrt_peer_attach": (C.c_int, [_H, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_int]),

@@ -51,3 +51,64 @@ class ChunkStorage:
         if c not in self.chunks:
             self.chunks[c] = PackedChunkData()
         return self.chunks[c]
+
+
+# ---- chunk files (src/world/chunk_storage.rs:37-68) ---------------------------------------------------------------
+def chunk_file_name(coord):
+    """{:016X}{:016X}{:016X} of the signed chunk coordinates (chunk_storage.rs:38-41)."""
+    import ctypes as C
+    from . import _native as N
+    buf = C.create_string_buffer(64)
+    assert N.lib.vxrt_chunk_file_name(int(coord[0]), int(coord[1]), int(coord[2]), buf, 64) == 0
+    return buf.value.decode()
+
+
+def encode_chunk(data):
+    """PackedChunkData -> bytes of the reference's chunk file (LZ4 frame of materials || minefield)."""
+    import ctypes as C
+    from . import _native as N
+    if data.minefield is None:
+        raise ValueError("a stored chunk carries its minefield (chunk_storage.rs:43-56)")
+    cap = N.lib.vxrt_chunk_encode_bound()
+    out = (C.c_uint8 * cap)()
+    n = C.c_size_t(0)
+    m = np.ascontiguousarray(data.materials, np.uint32); f = np.ascontiguousarray(data.minefield, np.uint8)
+    rc = N.lib.vxrt_chunk_encode(m.ctypes.data, f.ctypes.data, out, cap, C.byref(n))
+    if rc != 0:
+        raise ValueError(f"vxrt_chunk_encode failed ({rc})")
+    return bytes(out[:n.value])
+
+
+def decode_chunk(blob):
+    """bytes of a chunk file -> PackedChunkData (chunk_storage.rs:58-68)."""
+    from . import _native as N
+    m = np.empty((64, 64, 64), np.uint32); f = np.empty((64, 64, 64), np.uint8)
+    rc = N.lib.vxrt_chunk_decode(blob, len(blob), m.ctypes.data, f.ctypes.data)
+    if rc != 0:
+        raise ValueError(f"not a chunk file (vxrt_chunk_decode returned {rc})")
+    return PackedChunkData(m, f)
+
+
+class DiskChunkStorage(ChunkStorage):
+    """ChunkStorage backed by a directory of chunk files in the reference's format: a chunk missing from memory is
+    read from disk (chunk_storage.rs:118-141); `save` writes one.  Generation of missing chunks stays with the caller."""
+
+    def __init__(self, storage_dir):
+        super().__init__()
+        self.storage_dir = storage_dir
+
+    def path_for(self, coord):
+        import os
+        return os.path.join(self.storage_dir, chunk_file_name(coord))
+
+    def save(self, coord, data):
+        with open(self.path_for(coord), "wb") as fh:
+            fh.write(encode_chunk(data))
+
+    def borrow_packed_chunk_data(self, coord):
+        import os
+        c = tuple(coord)
+        if c not in self.chunks and os.path.exists(self.path_for(c)):
+            with open(self.path_for(c), "rb") as fh:
+                self.chunks[c] = decode_chunk(fh.read())
+        return super().borrow_packed_chunk_data(c)

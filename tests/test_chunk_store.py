@@ -1,0 +1,72 @@
+"""Chunk files in the reference's format (src/world/chunk_storage.rs:37-68): name = three {:016X}
+fields of the signed chunk coordinates, contents = LZ4 frame of materials (u32 LE) || minefield (u8).  The reference
+links liblz4 through the `lz4` crate; liblz4 is reachable here through pyarrow's "lz4" (frame) codec, so both
+directions are checked against the real library."""
+import numpy as np
+import pytest
+
+
+def _terrain_chunk(orc, seed):
+    rng = np.random.default_rng(seed)
+    z = np.arange(64)[:, None, None]
+    h = 20 + rng.integers(0, 12, size=(64, 64))
+    words = np.where(z < h[None], np.uint32(0x9F73D), np.uint32(0)).astype(np.uint32)
+    return orc.pack_chunk(words)
+
+
+def test_file_name_known_answers():
+    from raytrace_b200 import world as W
+    assert W.chunk_file_name((0, 0, 0)) == "0" * 48
+    assert W.chunk_file_name((1, 2, 255)) == "0000000000000001" "0000000000000002" "00000000000000FF"
+    assert W.chunk_file_name((-2, 0, 5)) == "FFFFFFFFFFFFFFFE" "0000000000000000" "0000000000000005"   # isize as two's complement
+
+
+def test_round_trip_and_liblz4_interop(orc):
+    pa = pytest.importorskip("pyarrow")
+    import raytrace_b200 as R
+    from raytrace_b200 import world as W
+    m, f = _terrain_chunk(orc, 0)
+    raw = m.astype("<u4").tobytes() + f.tobytes()
+    blob = W.encode_chunk(R.PackedChunkData(m, f))
+    assert len(blob) < len(raw) // 4                                   # terrain compresses
+    back = W.decode_chunk(blob)
+    assert np.array_equal(back.materials, m) and np.array_equal(back.minefield, f)
+    assert pa.decompress(blob, decompressed_size=len(raw), codec="lz4", asbytes=True) == raw      # liblz4 reads our frame
+    theirs = pa.compress(raw, codec="lz4", asbytes=True)              # linked 64 KiB blocks, as the lz4 crate writes
+    back = W.decode_chunk(theirs)
+    assert np.array_equal(back.materials, m) and np.array_equal(back.minefield, f)
+    rng = np.random.default_rng(1)                                     # incompressible -> stored block
+    m2 = rng.integers(0, 2 ** 32, size=(64, 64, 64), dtype=np.uint32); f2 = rng.integers(0, 256, size=(64, 64, 64), dtype=np.uint8)
+    b2 = W.encode_chunk(R.PackedChunkData(m2, f2))
+    back = W.decode_chunk(b2)
+    assert np.array_equal(back.materials, m2) and np.array_equal(back.minefield, f2)
+    assert pa.decompress(b2, decompressed_size=len(raw), codec="lz4", asbytes=True) == m2.astype("<u4").tobytes() + f2.tobytes()
+
+
+def test_bad_files_are_rejected(orc):
+    import raytrace_b200 as R
+    from raytrace_b200 import world as W
+    m, f = _terrain_chunk(orc, 2)
+    blob = W.encode_chunk(R.PackedChunkData(m, f))
+    for bad in (blob[:-3], blob[:200], b"\x00" * 64, blob[:4] + b"\xff" + blob[5:]):
+        with pytest.raises(ValueError):
+            W.decode_chunk(bad)
+    flipped = bytearray(blob); flipped[len(blob) // 2] ^= 0x10        # content checksum catches payload damage
+    with pytest.raises(ValueError):
+        W.decode_chunk(bytes(flipped))
+    with pytest.raises(ValueError):
+        W.encode_chunk(R.PackedChunkData(m, None))
+
+
+def test_disk_chunk_storage(orc, tmp_path):
+    """save -> new storage over the same directory -> borrow_packed_chunk_data reads the file; unknown chunks are air."""
+    import raytrace_b200 as R
+    from raytrace_b200 import world as W
+    m, f = _terrain_chunk(orc, 3)
+    st = W.DiskChunkStorage(str(tmp_path))
+    st.save((-1, 0, 2), R.PackedChunkData(m, f))
+    assert (tmp_path / ("F" * 16 + "0" * 16 + "0" * 15 + "2")).exists()
+    st2 = W.DiskChunkStorage(str(tmp_path))
+    got = st2.borrow_packed_chunk_data((-1, 0, 2))
+    assert np.array_equal(got.materials, m) and np.array_equal(got.minefield, f)
+    assert not st2.borrow_packed_chunk_data((9, 9, 9)).materials.any()
