@@ -11,79 +11,98 @@ namespace {
 // ---------------------------------------------------------------------------------------------
 // pack_into: per 64^3 chunk, minefield = 0 for solid voxels (bit 15), else the smallest k in 1..6
 // whose 2^k-aligned cube contains a solid voxel; a wholly empty chunk becomes all 6 / words 0.
-// One 512-thread block per chunk; the six "any solid" levels live in shared memory as bytes.
+// One 512-thread block per chunk.  The words are read ONCE, 16 bytes per thread and load; the solid bits of a voxel
+// row (64 voxels along x) are one 64-bit mask in shared memory, and level k is kept as masks at (y,z) resolution 2^k
+// with x left expanded (bit x = "the 2^k-cube containing x holds a solid"), so a level is three ORs of the level below
+// plus one in-word spread.  The levels are nested (solid in L1 in L2 ...), hence
+// minefield(x) = 6 - #{S, L1..L5 with bit x set}: four voxels are a byte-wise sum of six spread nibbles and one
+// 4-byte store.  HBM traffic: 4 B read + 1 B written per voxel (+4 B written when an empty chunk has to be wiped).
 // ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long spread_or(unsigned long long m, int shift, unsigned long long hi_mask) {
+    return m | ((m & hi_mask) >> shift) | ((m & ~hi_mask) << shift);      // OR of the two halves of every aligned 2*shift-bit group
+}
+__device__ __forceinline__ uint32_t nibble_to_bytes(uint32_t n) { return (n * 0x00204081u) & 0x01010101u; }   // bit i -> byte i
+
 __global__ void __launch_bounds__(512) k_build_minefield(uint32_t* __restrict__ materials, uint8_t* __restrict__ minefield,
                                                          int nx, int ny, int nz, const uint32_t* __restrict__ dirty) {
     if (dirty && !dirty[blockIdx.x]) return;
-    __shared__ uint8_t l1[32 * 32 * 32];
-    __shared__ uint8_t l2[16 * 16 * 16];
-    __shared__ uint8_t l3[8 * 8 * 8];
-    __shared__ uint8_t l4[4 * 4 * 4];
-    __shared__ uint8_t l5[2 * 2 * 2];
-    __shared__ uint8_t l6[1];
+    __shared__ unsigned long long S[64 * 64];                // solid bits of voxel row (z, y)
+    __shared__ unsigned long long L1[32 * 32], L2[16 * 16], L3[8 * 8], L4[4 * 4], L5[2 * 2];
+    __shared__ uint32_t s_any_solid, s_any_word;
     const int cxn = nx >> 6, cyn = ny >> 6;
     const int cx = blockIdx.x % cxn, cy = (blockIdx.x / cxn) % cyn, cz = blockIdx.x / (cxn * cyn);
     const size_t base = ((size_t)(cz * 64) * ny + cy * 64) * nx + cx * 64;
     const int tid = threadIdx.x;
-    for (int i = tid; i < 32 * 32 * 32 / 4; i += 512) reinterpret_cast<uint32_t*>(l1)[i] = 0;
-    for (int i = tid; i < 16 * 16 * 16 / 4; i += 512) reinterpret_cast<uint32_t*>(l2)[i] = 0;
-    if (tid < 128) reinterpret_cast<uint32_t*>(l3)[tid] = 0;
-    if (tid < 16) reinterpret_cast<uint32_t*>(l4)[tid] = 0;
-    if (tid < 8) l5[tid] = 0;
-    if (tid == 0) l6[0] = 0;
+    uint32_t* S32 = reinterpret_cast<uint32_t*>(S);
+    for (int i = tid; i < 64 * 64 * 2; i += 512) S32[i] = 0;
+    if (tid == 0) { s_any_solid = 0; s_any_word = 0; }
     __syncthreads();
-    // level 1 straight from the words (x fastest -> coalesced 256 B rows)
-    for (int v = tid; v < 64 * 64 * 64; v += 512) {
-        const int x = v & 63, y = (v >> 6) & 63, z = v >> 12;
-        const uint32_t w = materials[base + ((size_t)z * ny + y) * nx + x];
-        if ((w >> 15) & 1u) l1[((z >> 1) * 32 + (y >> 1)) * 32 + (x >> 1)] = 1;
+    // pass 1: four voxels per load; q = z*1024 + y*16 + x4
+    uint32_t any_word = 0, any_solid = 0;
+#pragma unroll 8
+    for (int it = 0; it < 128; it++) {
+        const int q = tid + it * 512, x4 = q & 15, y = (q >> 4) & 63, z = q >> 10;
+        const uint4 w = __ldcs(reinterpret_cast<const uint4*>(materials + base + ((size_t)z * ny + y) * nx + x4 * 4));
+        const uint32_t nib = ((w.x >> 15) & 1u) | ((w.y >> 14) & 2u) | ((w.z >> 13) & 4u) | ((w.w >> 12) & 8u);
+        any_word |= w.x | w.y | w.z | w.w;
+        any_solid |= nib;
+        if (nib) atomicOr(&S32[(z * 64 + y) * 2 + (x4 >> 3)], nib << ((x4 & 7) * 4));
+    }
+    if (__any_sync(0xffffffffu, any_solid != 0) && (tid & 31) == 0) s_any_solid = 1;
+    if (__any_sync(0xffffffffu, any_word != 0) && (tid & 31) == 0) s_any_word = 1;
+    __syncthreads();
+    const bool empty = s_any_solid == 0;                                        // chunk.rs:155-161
+    if (empty) {
+        // wholly empty chunk: every voxel 6, every word 0 (written only if some word is not already 0)
+        const bool wipe = s_any_word != 0;
+        for (int it = 0; it < 128; it++) {
+            const int q = tid + it * 512, x4 = q & 15, y = (q >> 4) & 63, z = q >> 10;
+            const size_t gi = base + ((size_t)z * ny + y) * nx + x4 * 4;
+            *reinterpret_cast<uint32_t*>(minefield + gi) = 0x06060606u;
+            if (wipe) *reinterpret_cast<uint4*>(materials + gi) = make_uint4(0, 0, 0, 0);
+        }
+        return;
+    }
+    // levels: OR of the 2x2 rows below, then the in-word spread of that level's group size
+    for (int c = tid; c < 32 * 32; c += 512) {
+        const int y = c & 31, z = c >> 5;
+        const unsigned long long m = S[(2 * z) * 64 + 2 * y] | S[(2 * z) * 64 + 2 * y + 1] | S[(2 * z + 1) * 64 + 2 * y] | S[(2 * z + 1) * 64 + 2 * y + 1];
+        L1[c] = spread_or(m, 1, 0xAAAAAAAAAAAAAAAAull);
     }
     __syncthreads();
-    for (int c = tid; c < 16 * 16 * 16; c += 512) {
-        const int x = c & 15, y = (c >> 4) & 15, z = c >> 8;
-        uint8_t any = 0;
-        for (int k = 0; k < 8; k++) any |= l1[((2 * z + (k >> 2)) * 32 + 2 * y + ((k >> 1) & 1)) * 32 + 2 * x + (k & 1)];
-        l2[c] = any;
+    if (tid < 16 * 16) {
+        const int y = tid & 15, z = tid >> 4;
+        const unsigned long long m = L1[(2 * z) * 32 + 2 * y] | L1[(2 * z) * 32 + 2 * y + 1] | L1[(2 * z + 1) * 32 + 2 * y] | L1[(2 * z + 1) * 32 + 2 * y + 1];
+        L2[tid] = spread_or(m, 2, 0xCCCCCCCCCCCCCCCCull);
     }
     __syncthreads();
-    if (tid < 512) {
-        const int x = tid & 7, y = (tid >> 3) & 7, z = tid >> 6;
-        uint8_t any = 0;
-        for (int k = 0; k < 8; k++) any |= l2[((2 * z + (k >> 2)) * 16 + 2 * y + ((k >> 1) & 1)) * 16 + 2 * x + (k & 1)];
-        l3[tid] = any;
+    if (tid < 8 * 8) {
+        const int y = tid & 7, z = tid >> 3;
+        const unsigned long long m = L2[(2 * z) * 16 + 2 * y] | L2[(2 * z) * 16 + 2 * y + 1] | L2[(2 * z + 1) * 16 + 2 * y] | L2[(2 * z + 1) * 16 + 2 * y + 1];
+        L3[tid] = spread_or(m, 4, 0xF0F0F0F0F0F0F0F0ull);
     }
     __syncthreads();
-    if (tid < 64) {
-        const int x = tid & 3, y = (tid >> 2) & 3, z = tid >> 4;
-        uint8_t any = 0;
-        for (int k = 0; k < 8; k++) any |= l3[((2 * z + (k >> 2)) * 8 + 2 * y + ((k >> 1) & 1)) * 8 + 2 * x + (k & 1)];
-        l4[tid] = any;
+    if (tid < 4 * 4) {
+        const int y = tid & 3, z = tid >> 2;
+        const unsigned long long m = L3[(2 * z) * 8 + 2 * y] | L3[(2 * z) * 8 + 2 * y + 1] | L3[(2 * z + 1) * 8 + 2 * y] | L3[(2 * z + 1) * 8 + 2 * y + 1];
+        L4[tid] = spread_or(m, 8, 0xFF00FF00FF00FF00ull);
     }
     __syncthreads();
-    if (tid < 8) {
-        const int x = tid & 1, y = (tid >> 1) & 1, z = tid >> 2;
-        uint8_t any = 0;
-        for (int k = 0; k < 8; k++) any |= l4[((2 * z + (k >> 2)) * 4 + 2 * y + ((k >> 1) & 1)) * 4 + 2 * x + (k & 1)];
-        l5[tid] = any;
+    if (tid < 2 * 2) {
+        const int y = tid & 1, z = tid >> 1;
+        const unsigned long long m = L4[(2 * z) * 4 + 2 * y] | L4[(2 * z) * 4 + 2 * y + 1] | L4[(2 * z + 1) * 4 + 2 * y] | L4[(2 * z + 1) * 4 + 2 * y + 1];
+        L5[tid] = spread_or(m, 16, 0xFFFF0000FFFF0000ull);
     }
     __syncthreads();
-    if (tid == 0) { uint8_t any = 0; for (int k = 0; k < 8; k++) any |= l5[k]; l6[0] = any; }
-    __syncthreads();
-    const bool empty = !l6[0];                                                  // chunk.rs:155-161
-    for (int v = tid; v < 64 * 64 * 64; v += 512) {
-        const int x = v & 63, y = (v >> 6) & 63, z = v >> 12;
-        const size_t gi = base + ((size_t)z * ny + y) * nx + x;
-        uint8_t mf;
-        if (empty) { materials[gi] = 0; mf = 6; }
-        else if ((materials[gi] >> 15) & 1u) mf = 0;
-        else if (l1[((z >> 1) * 32 + (y >> 1)) * 32 + (x >> 1)]) mf = 1;
-        else if (l2[((z >> 2) * 16 + (y >> 2)) * 16 + (x >> 2)]) mf = 2;
-        else if (l3[((z >> 3) * 8 + (y >> 3)) * 8 + (x >> 3)]) mf = 3;
-        else if (l4[((z >> 4) * 4 + (y >> 4)) * 4 + (x >> 4)]) mf = 4;
-        else if (l5[((z >> 5) * 2 + (y >> 5)) * 2 + (x >> 5)]) mf = 5;
-        else mf = 6;
-        minefield[gi] = mf;
+    // pass 2: minefield(x) = 6 - #{S, L1..L5 with bit x set}
+#pragma unroll 4
+    for (int it = 0; it < 128; it++) {
+        const int q = tid + it * 512, x4 = q & 15, y = (q >> 4) & 63, z = q >> 10;
+        const int sh = x4 * 4;
+        const uint32_t cnt = nibble_to_bytes((uint32_t)(S[z * 64 + y] >> sh) & 15u) + nibble_to_bytes((uint32_t)(L1[(z >> 1) * 32 + (y >> 1)] >> sh) & 15u) +
+                             nibble_to_bytes((uint32_t)(L2[(z >> 2) * 16 + (y >> 2)] >> sh) & 15u) + nibble_to_bytes((uint32_t)(L3[(z >> 3) * 8 + (y >> 3)] >> sh) & 15u) +
+                             nibble_to_bytes((uint32_t)(L4[(z >> 4) * 4 + (y >> 4)] >> sh) & 15u) + nibble_to_bytes((uint32_t)(L5[(z >> 5) * 2 + (y >> 5)] >> sh) & 15u);
+        __stcs(reinterpret_cast<uint32_t*>(minefield + base + ((size_t)z * ny + y) * nx + x4 * 4), 0x06060606u - cnt);
     }
 }
 
