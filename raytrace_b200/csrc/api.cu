@@ -69,6 +69,18 @@ void diffuse_luts(float* lut) {
     }
 }
 
+// (E12) trace_fast.cu: values the shader computes from small integers, tabulated with the shader's own sequence of
+// IEEE single-precision operations (volatile keeps the host compiler from contracting or widening them)
+void value_tables(float* lut, int width, int height) {
+    for (int n = 0; n < 256; n++) { volatile float q = (float)n / 255.0f; volatile float j = q * 0.05f; lut[VXRT_LUT_JITTER + n] = j; }
+    for (int n = 0; n < 128; n++) { volatile float q = (float)n / 127.0f; lut[VXRT_LUT_ALBEDO + n] = q; }
+    for (int a = 0; a < 2; a++) {
+        const int n = a ? height : width;
+        float* t = lut + VXRT_LUT_SCREEN + (a ? width : 0);
+        for (int i = 0; i < n; i++) { volatile float q = (float)i / (float)n; volatile float m = q * 2.0f; volatile float r = m - 1.0f; t[i] = r; }
+    }
+}
+
 // (E8) trace_fast.cu: g(p) = fl(p - lr) is monotone in p, so {p : |g(p)| >= H} = {p <= lo} U {p >= hi}.
 // lo/hi are found by bisection over the floats in their numeric order.
 uint32_t float_key(float f) { uint32_t u; memcpy(&u, &f, 4); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
@@ -305,10 +317,11 @@ int vxrt_create(const VxrtConfig* cfg, VxrtHandle** out) {
         if ((rc = alloc_zero(h, (void**)&h->d_noise, h->h_noise.size()))) return rc;
         if ((rc = alloc_zero(h, (void**)&h->d_dirty, (size_t)(cfg->nx >> 6) * (cfg->ny >> 6) * (cfg->nz >> 6) * 4))) return rc;
         if ((rc = alloc_zero(h, (void**)&h->d_counters, 8 * sizeof(unsigned long long)))) return rc;
-        CU(cudaMalloc((void**)&h->d_lut, 1024 * sizeof(float)));
-        float lut[1024];
-        diffuse_luts(lut);
-        CU(cudaMemcpyAsync(h->d_lut, lut, sizeof lut, cudaMemcpyHostToDevice, h->stream));
+        std::vector<float> lut((size_t)VXRT_LUT_SCREEN + cfg->width + cfg->height);
+        CU(cudaMalloc((void**)&h->d_lut, lut.size() * sizeof(float)));
+        diffuse_luts(lut.data());
+        value_tables(lut.data(), cfg->width, cfg->height);
+        CU(cudaMemcpyAsync(h->d_lut, lut.data(), lut.size() * sizeof(float), cudaMemcpyHostToDevice, h->stream));
         CU(cudaStreamSynchronize(h->stream));
         if ((rc = alloc_zero(h, (void**)&h->d_lighting, P * 8))) return rc;
         if ((rc = alloc_zero(h, (void**)&h->d_depth, P * 2))) return rc;

@@ -164,10 +164,10 @@ __global__ void __launch_bounds__(128) k_trace_general(const __grid_constant__ T
             light = f3(fdiv(a.x, a.w), fdiv(a.y, a.w), fdiv(a.z, a.w));
         }
         // G-buffer stores, :352-385 (formats render_data.rs:166-189)
-        P.lighting[pi] = make_ushort4((unsigned short)unorm_store(fdiv(light.x, 16.0f), 65535.0f),
-                                      (unsigned short)unorm_store(fdiv(light.y, 16.0f), 65535.0f),
-                                      (unsigned short)unorm_store(fdiv(light.z, 16.0f), 65535.0f),
-                                      (unsigned short)unorm_store(fdiv(1.0f, 16.0f), 65535.0f));
+        P.lighting[pi] = make_ushort4((unsigned short)unorm_store(fmul(light.x, 0.0625f), 65535.0f),
+                                      (unsigned short)unorm_store(fmul(light.y, 0.0625f), 65535.0f),
+                                      (unsigned short)unorm_store(fmul(light.z, 0.0625f), 65535.0f),
+                                      (unsigned short)unorm_store(0.0625f, 65535.0f));
         uint32_t d = 0xFFFF;
         if (!primary.air) d = __float2uint_rz(fmul(length3(sub3(origin, primary.position)), 32.0f));
         P.depth[pi] = (uint16_t)d;
@@ -177,8 +177,8 @@ __global__ void __launch_bounds__(128) k_trace_general(const __grid_constant__ T
                                    (unsigned char)unorm_store(alb.z, 255.0f), 255);
         P.emission[pi] = make_uchar4(0, 0, 0, primary.air ? 0 : 255);
         const F3 fogc = sample_sky(ray_dir, sunangle, sunlight, false);
-        P.fog[pi] = make_uchar4((unsigned char)unorm_store(fdiv(fogc.x, 2.0f), 255.0f), (unsigned char)unorm_store(fdiv(fogc.y, 2.0f), 255.0f),
-                                (unsigned char)unorm_store(fdiv(fogc.z, 2.0f), 255.0f), 255);
+        P.fog[pi] = make_uchar4((unsigned char)unorm_store(fmul(fogc.x, 0.5f), 255.0f), (unsigned char)unorm_store(fmul(fogc.y, 0.5f), 255.0f),
+                                (unsigned char)unorm_store(fmul(fogc.z, 0.5f), 255.0f), 255);
         if (P.hit_voxel) {
             P.hit_voxel[pi * 3] = primary.vx; P.hit_voxel[pi * 3 + 1] = primary.vy; P.hit_voxel[pi * 3 + 2] = primary.vz;
             P.hit_face[pi] = primary.air ? 16 : (uint8_t)primary.normal;

@@ -67,6 +67,8 @@ __device__ __forceinline__ uchar4 noise_texel(const uint8_t* bn, float cx, float
     ix = min(max(ix, 0), VXRT_NOISE_SIZE - 1); iy = min(max(iy, 0), VXRT_NOISE_SIZE - 1);
     return __ldg(reinterpret_cast<const uchar4*>(bn) + iy * VXRT_NOISE_SIZE + ix);
 }
-__device__ __forceinline__ float gmod512(float x) { return fsub(x, fmul(512.0f, floorf(fdiv(x, 512.0f)))); }
+// (E11) x / 2^k and x * 2^-k are the correctly rounded value of the same real number (denormal results included), so a
+// division by 2, 16 or 512 is written as the multiplication: one FMUL instead of the ~12-instruction IEEE division.
+__device__ __forceinline__ float gmod512(float x) { return fsub(x, fmul(512.0f, floorf(fmul(x, 0.001953125f)))); }
 
 }  // namespace

@@ -10,6 +10,10 @@
 #define VXRT_PEER_MAX_RANKS 16
 #define VXRT_PEER_MAX_LINKS 16
 #define VXRT_CHUNK 64
+// value tables behind the four diffuse tables in TraceParams::lut (api.cu value_tables; trace_fast.cu (E12))
+#define VXRT_LUT_JITTER 1024            // [256] n / 255 * 0.05   (raytrace.comp:186)
+#define VXRT_LUT_ALBEDO 1280            // [128] n / 127          (:156-158)
+#define VXRT_LUT_SCREEN 1408            // [width] px / width * 2 - 1, then [height] py / height * 2 - 1   (:296-297)
 
 // Per-frame constants handed to the kernels by value (fits the 4 KB parameter space).
 struct TraceParams {
@@ -34,7 +38,7 @@ struct TraceParams {
     const uint8_t* minefield;            // linear [nz][ny][nx]
     const uint32_t* materials;           // linear [nz][ny][nx]
     const uint8_t* noise;                // 512*512*4
-    const float* lut;                    // 4*256: sin1, cos1, sin2, cos2 (raytrace.comp:190-197)
+    const float* lut;                    // 4*256: sin1, cos1, sin2, cos2 (raytrace.comp:190-197), then the VXRT_LUT_* tables
     ushort4* lighting; uint16_t* depth; uint8_t* normal; uchar4* albedo; uchar4* emission; uchar4* fog;
     int32_t* hit_voxel; uint8_t* hit_face; uint32_t* hit_word; float* hit_t; uint32_t* steps; uint8_t* rays;
     float4* accum;
