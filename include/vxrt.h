@@ -232,6 +232,13 @@ int  vxrt_peer_attach(VxrtHandle* h, const void* blobs, size_t nbytes, int rank,
  * align the ranks before a timed frame. */
 int  vxrt_peer_barrier(VxrtHandle* h);
 
+/* ---- self test ---------------------------------------------------------------------------------------
+ * The trace kernel writes IEEE divisions that share a divisor as one refined reciprocal plus two FMAs per quotient
+ * (trace_fast.cu (E13)).  This runs that sequence and __fdiv_rn on n pseudo-random operand sets inside the guarded
+ * range on `device` and returns the number of results that differ in any bit (must be 0).  Test hook: the
+ * reference has no counterpart. */
+int  vxrt_selftest_division(int device, uint64_t n, uint64_t seed, uint64_t* mismatches);
+
 #ifdef __cplusplus
 }
 #endif

@@ -104,6 +104,7 @@ SYMBOLS = {
     "vxrt_peer_export": (C.c_int, [_H, C.c_void_p, C.c_size_t]),
     "vxrt_peer_barrier": (C.c_int, [_H]),
     "vxrt_peer_attach": (C.c_int, [_H, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_int]),
+    "vxrt_selftest_division": (C.c_int, [C.c_int, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64)]),
 }
 COMM_ID_BYTES = 128
 PEER_BLOB_BYTES = 512

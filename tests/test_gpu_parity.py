@@ -479,3 +479,15 @@ def test_row_costs_and_balanced_bands(orc, world, noise):
     finally:
         for r in rs:
             r.close()
+
+
+def test_refined_division_is_ieee_division():
+    """trace_fast.cu (E13): the shared-reciprocal quotient sequence equals __fdiv_rn bit for bit on 2^27 operand
+    sets inside the guarded range (three normalize quotients, one free quotient and three reciprocals each)."""
+    import ctypes as C
+    from raytrace_b200 import _native as N
+    lib = N.load()
+    for seed in (1, 0x9E3779B97F4A7C15):
+        bad = C.c_uint64(123)
+        assert lib.vxrt_selftest_division(0, 1 << 27, seed, C.byref(bad)) == N.OK
+        assert bad.value == 0
