@@ -539,6 +539,13 @@ int vxrt_render_frame(VxrtHandle* h) {
     H3 sd, sl;
     sun_constants(f.sun_angle, &sd, &sl);
     P.sun_x = sd.x; P.sun_y = sd.y; P.sun_z = sd.z; P.sl_r = sl.x; P.sl_g = sl.y; P.sl_b = sl.z;
+    {   // sample_sky's per-frame terms (raytrace.comp:272-274, :279); colour only
+        float s = ((sl.x + sl.y) + sl.z) * 0.2f - 0.02f;
+        s = s < 0.0f ? 0.0f : (s > 1.0f ? 1.0f : s);
+        P.sky_horizon_exp_half = 0.5f * (40.0f * (1.0f - s) + 10.0f * s);
+        P.sky_halo_exp = 5.0f * (1.0f - s) + 1.0f * s;
+        P.sky_bright_scale = s > 0.1f ? s : 0.1f;
+    }
     {   // raytrace.comp:298-303: texel (seed % 512, seed / 512), clamp-to-edge (render_data.rs:110-128)
         uint32_t ix = f.seed % VXRT_NOISE_SIZE, iy = f.seed / VXRT_NOISE_SIZE;
         if (iy > VXRT_NOISE_SIZE - 1) iy = VXRT_NOISE_SIZE - 1;

@@ -22,6 +22,8 @@ struct TraceParams {
     float lrx, lry, lrz;                 // window centre as float (raytrace.comp:104)
     float sun_x, sun_y, sun_z;           // raytrace.comp:317, evaluated once on the host
     float sl_r, sl_g, sl_b;              // sun_color(), raytrace.comp:318
+    // sample_sky terms that depend only on the sun (:272-274, :279): mix(40,10,sl)/2, mix(5,1,sl), max(sl,0.1)
+    float sky_horizon_exp_half, sky_halo_exp, sky_bright_scale;
     float noise_base_x, noise_base_y;    // raytrace.comp:302-303
     // geometry
     int width, height, row0, row1;       // rows [row0,row1) are traced
