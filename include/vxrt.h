@@ -42,6 +42,9 @@ typedef enum VxrtMode { VXRT_MODE_PRIMARY = 0, VXRT_MODE_SHADOW = 1, VXRT_MODE_F
 #define VXRT_FLAG_PONG_SWAP     0x10u /* reproduce descriptor_sets.rs:37-39 (odd passes read swapped images)*/
 #define VXRT_FLAG_GENERAL_MARCH 0x40u /* force the general march kernel (normally chosen per frame when a coordinate
                                          could reach 2^21 or the window has more than 2^32 voxels)               */
+#define VXRT_FLAG_REPROJECT     0x80u /* temporal reprojection under camera motion (extension): reads the
+                                         frame block's old_origin / old_transform_c0..2, which the reference fills every
+                                         frame (pipeline.rs:213-227) and its shaders never read; see vxrt_reset_history */
 #define VXRT_FLAG_REF_ROWS      0x20u /* leave the rows the reference grid (W/8,H/8+1) never writes untouched*/
 
 /* Replaces the compile-time constants of src/render/constants.rs:9-10,22-31 and the
@@ -69,10 +72,10 @@ typedef struct VxrtFrameParams {
     float    forward[3]; uint32_t _padding2;   /*  32 */
     float    up[3];      uint32_t _padding3;   /*  48  (pre-scaled by 0.4, pipeline.rs:198) */
     float    right[3];   uint32_t _padding4;   /*  64  (pre-scaled by 0.4, pipeline.rs:199) */
-    float    old_origin[3];       uint32_t _padding5;  /*  80  unread by the shaders */
-    float    old_transform_c0[3]; uint32_t _padding6;  /*  96  unread */
-    float    old_transform_c1[3]; uint32_t _padding7;  /* 112  unread */
-    float    old_transform_c2[3]; uint32_t _padding8;  /* 128  unread */
+    float    old_origin[3];       uint32_t _padding5;  /*  80  unread by the reference shaders; read by VXRT_FLAG_REPROJECT */
+    float    old_transform_c0[3]; uint32_t _padding6;  /*  96  columns of inverse([right*0.4 | up*0.4 | forward]) of the */
+    float    old_transform_c1[3]; uint32_t _padding7;  /* 112  previous frame (pipeline.rs:215-226); unread by the        */
+    float    old_transform_c2[3]; uint32_t _padding8;  /* 128  reference shaders; read by VXRT_FLAG_REPROJECT            */
     int32_t  region_offset[3];    uint32_t _padding9;  /* 144  unread */
     int32_t  rotation[3];         uint32_t _padding10; /* 160  shader name: lr (window centre) */
     int32_t  space_offset[3];     uint32_t _padding11; /* 176  unread */
@@ -97,6 +100,10 @@ typedef enum VxrtBufferId {
     VXRT_BUF_RAYS = 12,      /* u8      w*h     trace_ray calls of the pixel                   */
     VXRT_BUF_ACCUM = 13,     /* f32x4   w*h*16  running sum of light + frame count             */
     VXRT_BUF_LIGHTING_RAW = 14, /* RGBA16 w*h*8 lighting as written by the trace pass          */
+    VXRT_BUF_HIT_POS = 15,   /* f32x4   w*h*16  primary.position after the :166-180 offset, w = bits of the int face
+                                                code; {0,0,0,16} on air (REPROJECT)                               */
+    VXRT_BUF_HISTORY = 16,   /* f32x4   w*h*16  mean light over the reprojected samples + sample count (REPROJECT) */
+    VXRT_BUF_COMPLETED = 17, /* RGBA16  w*h*8   completed_buffer (raytrace.comp:19): mean/16, a = count/MAX_SAMPLES */
     VXRT_BUF_COUNT_
 } VxrtBufferId;
 
@@ -154,6 +161,17 @@ int  vxrt_render_frame(VxrtHandle* h);
 /* replaces wait_for_fences (pipeline.rs:162-172) */
 int  vxrt_sync(VxrtHandle* h);
 int  vxrt_reset_accumulation(VxrtHandle* h);
+/* Temporal reprojection (VXRT_FLAG_REPROJECT; extension — the reference only prepares its inputs).  Between the trace
+ * pass and the denoise passes, per pixel:
+ *   L = lighting texel * 16;  n = 0, Hm = 0
+ *   hit: r = primary.position - old_origin; v = c0*r.x + c1*r.y + c2*r.z; if v.z > 0: f = ((v.xy/v.z + 1) * 0.5) * (W,H),
+ *        q = floor(f + 0.5); if q is inside the frame and the previous frame's hit at q has the same face code and the
+ *        same floor(position): n = min(count_prev(q), MAX_SAMPLES - 1), Hm = mean_prev(q)        (MAX_SAMPLES = 8)
+ *   mean = (Hm*n + L) / (n + 1);  history = {mean, n + 1};  lighting = mean / 16;  completed = {mean / 16, (n+1)/8}
+ * so a pixel that sees the same voxel face as the previous frame keeps up to 8 frames of light, and a disoccluded
+ * one starts again at 1.  The whole frame must live on one handle (no row bands, no peer mode) and the flag excludes
+ * VXRT_FLAG_ACCUMULATE.  vxrt_reset_history forgets the previous frame (camera cut, world edit). */
+int  vxrt_reset_history(VxrtHandle* h);
 
 /* ---- output ------------------------------------------------------------------------- */
 /* replaces queue_present (pipeline.rs:237-254): the frame is a headless device buffer. */

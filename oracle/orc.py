@@ -31,7 +31,7 @@ class OrcBuffers(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("lighting", C.c_void_p), ("depth", C.c_void_p),
                 ("normal", C.c_void_p), ("albedo", C.c_void_p), ("emission", C.c_void_p), ("fog", C.c_void_p),
                 ("hit_voxel", C.c_void_p), ("hit_face", C.c_void_p), ("hit_word", C.c_void_p), ("hit_t", C.c_void_p),
-                ("steps", C.c_void_p), ("rays", C.c_void_p), ("accum", C.c_void_p)]
+                ("steps", C.c_void_p), ("rays", C.c_void_p), ("accum", C.c_void_p), ("hit_pos", C.c_void_p)]
 
 
 class OrcStats(C.Structure):
@@ -58,6 +58,10 @@ def lib():
         L.orc_build_minefield.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int]
         L.orc_fill_frame.restype = None
         L.orc_fill_frame.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_uint32, C.c_void_p]
+        L.orc_fill_old_transform.restype = None
+        L.orc_fill_old_transform.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_reproject.restype = None
+        L.orc_reproject.argtypes = [C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 6 + [C.c_int]
         L.orc_diffuse_luts.restype = None
         L.orc_diffuse_luts.argtypes = [C.c_void_p] * 4
         L.orc_trace.restype = C.c_int
@@ -139,6 +143,34 @@ def fill_frame(origin, heading, pitch, sun_angle, seed, lr=(0, 0, 0)):
     return block
 
 
+def fill_old_transform(next_block, prev_block):
+    """pipeline.rs:213-227: old_origin / old_transform_c0..2 of `next_block` from the frame submitted before it (in place)."""
+    assert next_block.dtype == np.uint8 and next_block.size == 192
+    lib().orc_fill_old_transform(_p(next_block), _p(np.ascontiguousarray(prev_block, np.uint8)))
+    return next_block
+
+
+class History:
+    """State of the temporal-reprojection extension between frames (double-buffered on the device; two arrays here)."""
+
+    def __init__(self, width, height):
+        self.hit_pos = np.zeros((height, width, 4), np.float32)     # previous frame's records
+        self.hist = np.zeros((height, width, 4), np.float32)        # previous frame's {mean rgb, count}
+        self.completed = np.zeros((height, width, 4), np.uint16)
+
+
+def reproject(frame_block, fr, history, threads=0):
+    """orc_reproject on Frame `fr` (needs fr.hit_pos) against `history`; updates both in place."""
+    h, w = fr.height, fr.width
+    cur = np.zeros_like(history.hist)
+    blk = np.ascontiguousarray(frame_block, np.uint8)
+    lib().orc_reproject(_p(blk), w, h, _p(fr.lighting), _p(fr.hit_pos), _p(history.hit_pos), _p(history.hist), _p(cur),
+                        _p(history.completed), threads)
+    history.hist = cur
+    history.hit_pos = fr.hit_pos.copy()
+    return history
+
+
 def diffuse_luts():
     t = [np.empty(256, np.float32) for _ in range(4)]
     lib().orc_diffuse_luts(*[_p(a) for a in t])
@@ -158,8 +190,9 @@ def trace_ray(materials, minefield, noise, lr, origin, direction, max_steps=2048
 class Frame:
     """All per-pixel outputs of one oracle frame (numpy arrays)."""
 
-    def __init__(self, width, height, accumulate=False):
+    def __init__(self, width, height, accumulate=False, hit_pos=False):
         P = (height, width)
+        self.hit_pos = np.zeros(P + (4,), np.float32) if hit_pos else None
         self.width, self.height = width, height
         self.lighting = np.zeros(P + (4,), np.uint16)
         self.depth = np.zeros(P, np.uint16)
@@ -181,20 +214,22 @@ class Frame:
     def buffers(self):
         return OrcBuffers(self.width, self.height, _p(self.lighting), _p(self.depth), _p(self.normal), _p(self.albedo),
                           _p(self.emission), _p(self.fog), _p(self.hit_voxel), _p(self.hit_face), _p(self.hit_word),
-                          _p(self.hit_t), _p(self.steps), _p(self.rays), _p(self.accum))
+                          _p(self.hit_t), _p(self.steps), _p(self.rays), _p(self.accum), _p(self.hit_pos))
 
 
 def render(materials, minefield, noise, frame_block, mode, width, height, *, denoise=False, finalize=False,
-           pong_swap=False, frame=None, rows=None, max_steps=2048, threads=0):
+           pong_swap=False, frame=None, rows=None, max_steps=2048, threads=0, history=None):
     """raytrace.comp -> [6x bilateral_denoise.comp] -> [finalize.comp] on the CPU (pipeline.rs:86-123)."""
     nz, ny, nx = minefield.shape
     sc = OrcScene(nx, ny, nz, _p(materials), _p(minefield), _p(noise), max_steps)
-    fr = frame if frame is not None else Frame(width, height)
+    fr = frame if frame is not None else Frame(width, height, hit_pos=history is not None)
     r0, r1 = rows if rows is not None else (0, height)
     b = fr.buffers()
     blk = np.ascontiguousarray(frame_block, np.uint8)
     lib().orc_trace(C.byref(sc), _p(blk), mode, C.byref(b), r0, r1, C.byref(fr.stats), threads)
     fr.lighting_raw = fr.lighting.copy()
+    if history is not None:                      # temporal reprojection (extension): between trace and denoise
+        reproject(blk, fr, history, threads)
     if denoise:
         pong = np.zeros_like(fr.lighting)
         for k, size in enumerate(DENOISE_SIZES):

@@ -54,6 +54,9 @@ typedef struct OrcBuffers {
     uint8_t*  rays;       /* w*h, number of trace_ray calls                   */
     /* temporal accumulation (extension): running SUM of fp32 light */
     float*    accum;      /* w*h*4 (rgb + unused)                             */
+    /* temporal reprojection (extension): primary.position (after the :166-180 offset)
+     * of a hit, w = bit pattern of the int face code; {0,0,0,16} on air */
+    float*    hit_pos;    /* w*h*4 */
 } OrcBuffers;
 
 typedef struct OrcStats {
@@ -76,6 +79,25 @@ void orc_build_minefield(uint32_t* materials, uint8_t* minefield, int nx, int ny
 /* util.rs:9-22 + pipeline.rs:195-207: fills a 192-byte RaytraceUniformData block. */
 void orc_fill_frame(uint8_t block[192], const float origin[3], float heading, float pitch,
                     float sun_angle, uint32_t seed, const int32_t lr[3]);
+
+/* pipeline.rs:213-227: after frame `prev` was submitted the host stores old_origin = origin and
+ * old_transform = inverse(from_cols(right*0.4, up*0.4, forward)) for the NEXT frame.  Writes those four fields of
+ * `next` from prev's origin/right/up/forward (the uniform block already holds right and up pre-scaled).
+ * Matrix3::invert restated from cgmath 0.17.0 (not in the tree): cofactor rows / determinant. */
+void orc_fill_old_transform(uint8_t next[192], const uint8_t prev[192]);
+
+/* Temporal reprojection (extension; finishes the vestiges raytrace.comp:19,31,58 + pipeline.rs:213-227).
+ * Per pixel, after the trace pass and before the denoise passes:
+ *   L = lighting texel * 16 (RGBA16_UNORM load); n = 0, Hm = 0
+ *   hit (face < 16): r = p - old_origin; v = c0*r.x + c1*r.y + c2*r.z (summed left to right);
+ *     if v.z > 0: s = v.xy / v.z; f = ((s + 1) * 0.5) * (W, H); q = floor(f + 0.5);
+ *     if q inside the image and the previous frame's record at q has the same face and the same floor(position):
+ *       n = min(count_prev(q), MAX_SAMPLES - 1), Hm = mean_prev(q)
+ *   mean = (Hm * n + L) / (n + 1); history_cur = {mean, n + 1}; lighting = store16(mean / 16);
+ *   completed = store16({mean / 16, (n + 1) / MAX_SAMPLES})
+ * hist_* are float4 per pixel {mean rgb, count}; hit_pos_* as OrcBuffers::hit_pos.  MAX_SAMPLES = 8 (raytrace.comp:58). */
+void orc_reproject(const uint8_t frame[192], int width, int height, uint16_t* lighting, const float* hit_pos_cur,
+                   const float* hit_pos_prev, const float* hist_prev, float* hist_cur, uint16_t* completed, int n_threads);
 
 /* 256-entry LUTs for diffuse_direction (raytrace.comp:190-197): per byte b,
  * sin/cos of theta1 = 2*pi*(b/255) and sin/cos of theta2 = acos(1-2*(b/255)). */

@@ -290,6 +290,12 @@ int orc_trace(const OrcScene* scene, const uint8_t frame[192], int mode, OrcBuff
                 }
                 if (out->hit_voxel) { out->hit_voxel[pi * 3] = primary.voxel[0]; out->hit_voxel[pi * 3 + 1] = primary.voxel[1]; out->hit_voxel[pi * 3 + 2] = primary.voxel[2]; }
                 if (out->hit_face) out->hit_face[pi] = primary.air ? 16 : (uint8_t)primary.normal;
+                if (out->hit_pos) {
+                    float* o = out->hit_pos + pi * 4;
+                    const int32_t fc = primary.air ? 16 : (int32_t)primary.normal;
+                    o[0] = primary.air ? 0.0f : primary.position.x; o[1] = primary.air ? 0.0f : primary.position.y;
+                    o[2] = primary.air ? 0.0f : primary.position.z; memcpy(o + 3, &fc, 4);
+                }
                 if (out->hit_word) out->hit_word[pi] = primary.air ? 0u : primary.word;
                 if (out->hit_t) out->hit_t[pi] = primary.distance;
                 if (out->steps) out->steps[pi] = (uint32_t)(st.steps - steps0);

@@ -117,6 +117,9 @@ BufDesc buffer_of(const VxrtHandle* h, int id) {
         case VXRT_BUF_RAYS: return {h->d_rays, h->d_rays ? P : 0};
         case VXRT_BUF_ACCUM: return {h->d_accum, h->d_accum ? P * 16 : 0};
         case VXRT_BUF_LIGHTING_RAW: return {h->d_lighting_raw, h->d_lighting_raw ? P * 8 : 0};
+        case VXRT_BUF_HIT_POS: return {h->d_hit_pos[h->hist_idx], h->d_hit_pos[0] ? P * 16 : 0};
+        case VXRT_BUF_HISTORY: return {h->d_hist[h->hist_idx], h->d_hist[0] ? P * 16 : 0};
+        case VXRT_BUF_COMPLETED: return {h->d_completed, h->d_completed ? P * 8 : 0};
         default: return {nullptr, 0};
     }
 }
@@ -266,6 +269,10 @@ int vxrt_create(const VxrtConfig* cfg, VxrtHandle** out) {
     int row0 = cfg->row_begin, row1 = cfg->row_end;
     if (row0 == 0 && row1 == 0) row1 = cfg->height;
     if (row0 < 0 || row1 > cfg->height || row0 >= row1) { g_create_error = "vxrt_create: bad row band"; return VXRT_ERR_INVALID; }
+    if (cfg->flags & VXRT_FLAG_REPROJECT) {
+        if (cfg->flags & VXRT_FLAG_ACCUMULATE) { g_create_error = "vxrt_create: VXRT_FLAG_REPROJECT excludes VXRT_FLAG_ACCUMULATE"; return VXRT_ERR_INVALID; }
+        if (row0 != 0 || row1 != cfg->height) { g_create_error = "vxrt_create: VXRT_FLAG_REPROJECT needs the whole frame on one handle"; return VXRT_ERR_INVALID; }
+    }
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0) {
@@ -302,7 +309,7 @@ int vxrt_create(const VxrtConfig* cfg, VxrtHandle** out) {
 
     auto init = [&]() -> int {
         // load every kernel now: a lazy load at first launch cannot complete while a peer-mode kernel spins on a flag
-        CU(vxrt_preload_trace()); CU(vxrt_preload_trace_fast()); CU(vxrt_preload_post()); CU(vxrt_preload_world()); CU(vxrt_preload_peer());
+        CU(vxrt_preload_trace()); CU(vxrt_preload_trace_fast()); CU(vxrt_preload_post()); CU(vxrt_preload_world()); CU(vxrt_preload_peer()); CU(vxrt_preload_temporal());
         CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
         for (int i = 0; i < 5; i++) CU(cudaEventCreate(&h->ev[i]));
         CU(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
@@ -343,6 +350,13 @@ int vxrt_create(const VxrtConfig* cfg, VxrtHandle** out) {
             if ((rc = alloc_zero(h, (void**)&h->d_lighting_raw, P * 8))) return rc;
         }
         if (cfg->flags & VXRT_FLAG_ACCUMULATE) if ((rc = alloc_zero(h, (void**)&h->d_accum, P * 16))) return rc;
+        if (cfg->flags & VXRT_FLAG_REPROJECT) {
+            for (int i = 0; i < 2; i++) {
+                if ((rc = alloc_zero(h, (void**)&h->d_hit_pos[i], P * 16))) return rc;
+                if ((rc = alloc_zero(h, (void**)&h->d_hist[i], P * 16))) return rc;
+            }
+            if ((rc = alloc_zero(h, (void**)&h->d_completed, P * 8))) return rc;
+        }
         CU(cudaStreamSynchronize(h->stream));
         return VXRT_OK;
     };
@@ -361,7 +375,8 @@ void vxrt_destroy(VxrtHandle* h) {
     vxrt_peer_release(h);
     void* ptrs[] = {h->d_materials, h->d_minefield, h->d_noise, h->d_lut, h->d_dirty, h->d_edits, h->d_lighting, h->d_pong,
                     h->d_lighting_raw, h->d_depth, h->d_normal, h->d_albedo, h->d_emission, h->d_fog, h->d_out_buf[0], h->d_out_buf[1],
-                    h->d_hit_voxel, h->d_hit_face, h->d_hit_word, h->d_hit_t, h->d_steps, h->d_rays, h->d_accum, h->d_counters};
+                    h->d_hit_voxel, h->d_hit_face, h->d_hit_word, h->d_hit_t, h->d_steps, h->d_rays, h->d_accum, h->d_counters,
+                    h->d_hit_pos[0], h->d_hit_pos[1], h->d_hist[0], h->d_hist[1], h->d_completed};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 5; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     for (int i = 0; i < 2; i++) {
@@ -522,6 +537,18 @@ int vxrt_reset_accumulation(VxrtHandle* h) {
     return VXRT_OK;
 }
 
+int vxrt_reset_history(VxrtHandle* h) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (!h->d_hist[0]) return fail(h, VXRT_ERR_STATE, "vxrt_reset_history: handle created without VXRT_FLAG_REPROJECT");
+    CU(cudaSetDevice(h->cfg.device));
+    // zeroed records read as "face 0 at the origin, 0 samples": a match contributes nothing
+    for (int i = 0; i < 2; i++) {
+        CU(cudaMemsetAsync(h->d_hit_pos[i], 0, pixels(h) * 16, h->stream));
+        CU(cudaMemsetAsync(h->d_hist[i], 0, pixels(h) * 16, h->stream));
+    }
+    return VXRT_OK;
+}
+
 int vxrt_render_frame(VxrtHandle* h) {
     if (!h) return VXRT_ERR_INVALID;
     if (!h->have_world) return fail(h, VXRT_ERR_STATE, "vxrt_render_frame: no world uploaded");
@@ -575,6 +602,8 @@ int vxrt_render_frame(VxrtHandle* h) {
     P.hit_voxel = h->d_hit_voxel; P.hit_face = h->d_hit_face; P.hit_word = h->d_hit_word; P.hit_t = h->d_hit_t;
     P.steps = h->d_steps; P.rays = h->d_rays;
     P.accum = h->d_accum;
+    if (h->d_hist[0]) h->hist_idx ^= 1;                                  // this frame's records; [hist_idx ^ 1] = the frame before
+    P.hit_pos = h->d_hit_pos[h->hist_idx];
     P.counters = h->d_counters;
 
     // the image goes to the buffer an asynchronous read-back is not using (vxrt_read_output_async)
@@ -609,6 +638,19 @@ int vxrt_render_frame(VxrtHandle* h) {
     if (h->d_lighting_raw)
         CU(cudaMemcpyAsync(h->d_lighting_raw, h->d_lighting, pixels(h) * 8, cudaMemcpyDeviceToDevice, h->stream));
     if (h->d_accum) h->frames_accumulated++;
+    if (h->d_hist[0]) {                                                  // temporal.cu; timed with the denoise passes
+        ReprojectParams R;
+        memset(&R, 0, sizeof R);
+        R.oox = f.old_origin[0]; R.ooy = f.old_origin[1]; R.ooz = f.old_origin[2];
+        R.c0x = f.old_transform_c0[0]; R.c0y = f.old_transform_c0[1]; R.c0z = f.old_transform_c0[2];
+        R.c1x = f.old_transform_c1[0]; R.c1y = f.old_transform_c1[1]; R.c1z = f.old_transform_c1[2];
+        R.c2x = f.old_transform_c2[0]; R.c2y = f.old_transform_c2[1]; R.c2z = f.old_transform_c2[2];
+        R.width = h->cfg.width; R.height = h->cfg.height;
+        R.lighting = h->d_lighting; R.completed = h->d_completed;
+        R.hit_pos_cur = h->d_hit_pos[h->hist_idx]; R.hit_pos_prev = h->d_hit_pos[h->hist_idx ^ 1];
+        R.hist_prev = h->d_hist[h->hist_idx ^ 1]; R.hist_cur = h->d_hist[h->hist_idx];
+        CU(vxrt_launch_reproject(R, h->stream));
+    }
     if (h->cfg.flags & VXRT_FLAG_DENOISE) {
         // pipeline.rs:98-115: even passes lighting -> pong, odd passes pong -> lighting.  A band shrinks
         // by 3*size rows per pass towards [row0,row1) so that only valid rows are ever read.

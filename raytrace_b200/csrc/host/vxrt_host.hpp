@@ -154,7 +154,19 @@ class Pipeline {
         check(h_, vxrt_set_frame(h_, &u));
         check(h_, vxrt_render_frame(h_));
         check(h_, vxrt_read_output(h_, frame_.data(), frame_.size()));
-        for (int i = 0; i < 3; i++) u.old_origin[i] = u.origin[i];                                   // pipeline.rs:213-214 (dead in the shaders)
+        // pipeline.rs:213-227: set after the submit, so it describes this frame to the next one (read by VXRT_FLAG_REPROJECT)
+        for (int i = 0; i < 3; i++) u.old_origin[i] = u.origin[i];
+        {   // cgmath 0.17.0 Matrix3::invert of from_cols(right*0.4, up*0.4, forward): cofactor rows / determinant, transposed
+            const float* a = u.right; const float* b = u.up; const float* c = u.forward;
+            auto cross = [](const float* p, const float* q, float* o) { o[0] = p[1] * q[2] - p[2] * q[1]; o[1] = p[2] * q[0] - p[0] * q[2]; o[2] = p[0] * q[1] - p[1] * q[0]; };
+            const float det = a[0] * (b[1] * c[2] - c[1] * b[2]) - b[0] * (a[1] * c[2] - c[1] * a[2]) + c[0] * (a[1] * b[2] - b[1] * a[2]);
+            float r0[3] = {0, 0, 0}, r1[3] = {0, 0, 0}, r2[3] = {0, 0, 0};
+            if (det != 0.0f) { cross(b, c, r0); cross(c, a, r1); cross(a, b, r2); for (int i = 0; i < 3; i++) { r0[i] /= det; r1[i] /= det; r2[i] /= det; } }
+            for (int k = 0; k < 3; k++) {
+                float* col = k == 0 ? u.old_transform_c0 : k == 1 ? u.old_transform_c1 : u.old_transform_c2;
+                col[0] = r0[k]; col[1] = r1[k]; col[2] = r2[k];
+            }
+        }
     }
     void set_render_offset(int x, int y, int z) { render_offset_[0] = x; render_offset_[1] = y; render_offset_[2] = z; }
     const std::vector<uint8_t>& frame() const { return frame_; }

@@ -315,6 +315,7 @@ int vxrt_peer_attach(VxrtHandle* h, const void* blobs, size_t nbytes, int rank, 
     }
     if (!blobs || nbytes < (size_t)nranks * VXRT_PEER_BLOB_BYTES) { h->err = "vxrt_peer_attach: need nranks blobs"; return VXRT_ERR_SIZE; }
     if (h->peer_on) { h->err = "vxrt_peer_attach: already attached"; return VXRT_ERR_STATE; }
+    if (h->cfg.flags & VXRT_FLAG_REPROJECT) { h->err = "vxrt_peer_attach: VXRT_FLAG_REPROJECT needs the whole frame on one handle"; return VXRT_ERR_INVALID; }
     if (!h->d_peer_flags) { h->err = "vxrt_peer_attach: vxrt_peer_export not called on this handle"; return VXRT_ERR_STATE; }
     CU(cudaSetDevice(h->cfg.device));
     std::vector<PeerBlob> all(nranks);

@@ -179,6 +179,9 @@ __global__ void __launch_bounds__(128) k_trace_general(const __grid_constant__ T
         const F3 fogc = sample_sky(ray_dir, sunangle, sunlight, false);
         P.fog[pi] = make_uchar4((unsigned char)unorm_store(fmul(fogc.x, 0.5f), 255.0f), (unsigned char)unorm_store(fmul(fogc.y, 0.5f), 255.0f),
                                 (unsigned char)unorm_store(fmul(fogc.z, 0.5f), 255.0f), 255);
+        if (P.hit_pos)                                                                       // record for k_reproject (temporal.cu)
+            P.hit_pos[pi] = primary.air ? make_float4(0.0f, 0.0f, 0.0f, __int_as_float(16))
+                                        : make_float4(primary.position.x, primary.position.y, primary.position.z, __int_as_float((int)primary.normal));
         if (P.hit_voxel) {
             P.hit_voxel[pi * 3] = primary.vx; P.hit_voxel[pi * 3 + 1] = primary.vy; P.hit_voxel[pi * 3 + 2] = primary.vz;
             P.hit_face[pi] = primary.air ? 16 : (uint8_t)primary.normal;

@@ -44,7 +44,16 @@ struct TraceParams {
     ushort4* lighting; uint16_t* depth; uint8_t* normal; uchar4* albedo; uchar4* emission; uchar4* fog;
     int32_t* hit_voxel; uint8_t* hit_face; uint32_t* hit_word; float* hit_t; uint32_t* steps; uint8_t* rays;
     float4* accum;
+    float4* hit_pos;                     // VXRT_FLAG_REPROJECT: primary.position (offset, :166-180) + face bits; {0,0,0,16} on air
     unsigned long long* counters;        // [0]=rays [1]=steps [2]=hits [3]=noise fetches [4]=limit exhausted
+};
+
+// temporal.cu: old_origin / old_transform_c0..2 of the frame block (pipeline.rs:213-227) and the images of the pass
+struct ReprojectParams {
+    float oox, ooy, ooz, c0x, c0y, c0z, c1x, c1y, c1z, c2x, c2y, c2z;
+    int width, height;
+    ushort4* lighting; ushort4* completed;
+    const float4* hit_pos_cur; const float4* hit_pos_prev; const float4* hist_prev; float4* hist_cur;
 };
 
 // one halo link of the peer-memory frame (peer.cu): rows [r0,r1) go to / come from `rank`
@@ -75,6 +84,8 @@ struct VxrtHandle {
     uint16_t* d_depth; uint8_t* d_normal; uchar4 *d_albedo, *d_emission, *d_fog, *d_output;
     int32_t* d_hit_voxel; uint8_t* d_hit_face; uint32_t* d_hit_word; float* d_hit_t; uint32_t* d_steps; uint8_t* d_rays;
     float4* d_accum;
+    // temporal reprojection (temporal.cu): hit records and {mean light, count} of this frame and the one before
+    float4* d_hit_pos[2] = {nullptr, nullptr}; float4* d_hist[2] = {nullptr, nullptr}; ushort4* d_completed = nullptr; int hist_idx = 0;
     unsigned long long* d_counters;
     VxrtFrameParams frame; bool have_frame, have_world, have_noise, rendered;
     uint32_t frames_accumulated;
@@ -103,7 +114,7 @@ int vxrt_peer_error_word(VxrtHandle* h, uint32_t* out);
 
 // module preload (cudaFuncGetAttributes on every kernel of a file)
 cudaError_t vxrt_preload_trace(); cudaError_t vxrt_preload_trace_fast(); cudaError_t vxrt_preload_post();
-cudaError_t vxrt_preload_world(); cudaError_t vxrt_preload_peer();
+cudaError_t vxrt_preload_world(); cudaError_t vxrt_preload_peer(); cudaError_t vxrt_preload_temporal();
 
 // launchers (each returns the cudaGetLastError() of its launch)
 cudaError_t vxrt_launch_trace(const TraceParams& p, cudaStream_t s);        // dispatches on p.fast
@@ -113,6 +124,7 @@ cudaError_t vxrt_launch_denoise(const ushort4* src, ushort4* dst, const uint16_t
 cudaError_t vxrt_launch_finalize(const uchar4* albedo, const uchar4* emission, const uchar4* fog, const ushort4* lighting,
                                  const uint16_t* depth, const uint8_t* noise, uchar4* out, int width, int height,
                                  int row0, int row1, cudaStream_t s, const VxrtPeerTail* tail = nullptr);
+cudaError_t vxrt_launch_reproject(const ReprojectParams& p, cudaStream_t s);
 cudaError_t vxrt_launch_row_cost(const uint32_t* steps, const uint8_t* rays, const uint8_t* normal, int width, int height,
                                  float* out /* 3 per row: steps, rays, filtered pixels */, cudaStream_t s);
 cudaError_t vxrt_launch_build_minefield(uint32_t* materials, uint8_t* minefield, int nx, int ny, int nz,
