@@ -3,9 +3,16 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl vxrt|reference] [--workload c2|c3|c1|c4|c5]
 
-A "step" is one frame of the workload's camera path: trace -> 6x denoise -> finalize (+ NCCL gather of the
-row bands at N > 1).  Default workload = BASELINE config 2: 1920x1080, primary + 1 shadow ray per pixel,
-512^3 seeded biome world, 64-frame camera path.  One JSON line is printed by rank 0.
+A "step" is one frame of the workload's camera path per GPU: trace -> 6x denoise -> finalize.  Default workload =
+BASELINE config 2: 1920x1080, primary + 1 shadow ray per pixel, 512^3 seeded biome world, 64-frame camera path.
+One JSON line is printed by rank 0.
+
+At N > 1 the frames of a camera path are independent units, so they are dealt round-robin to the GPUs (frame i on
+rank i % N; world replicated; each rank reads its frames back itself; no collective on the data path; "weak"
+scaling: a job-wide step is N frames).  The same run then also times the image-space split north_star describes — ONE
+frame cut into load-balanced row bands, halo rows and finished bands stored over NVLink peer memory — and reports it
+under `image_bands` ("strong" scaling: the latency of a frame).  Workloads whose frame k+1 depends on frame k (c3:
+temporal accumulation, c5: edit stream) only have the band form.  --shard frames|bands forces one of them.
 
   value  : Mrays/s over the whole step, world + frame block already resident in HBM, CUDA-event timed.
   e2e    : the same through the public call sequence with HOST buffers: vxrt_set_frame(192-byte host block)
@@ -56,16 +63,24 @@ def parse_args():
     ap.add_argument("--bands", default="balanced", choices=["balanced", "equal"],
                     help="N > 1: balanced = row bands from per-row work counters of three calibration frames "
                          "(vxrt_plan_bands_weighted); equal = equal-height bands")
+    ap.add_argument("--shard", default="auto", choices=["auto", "frames", "bands"],
+                    help="N > 1: frames = the frames of the camera path are dealt round-robin to the GPUs, each renders whole "
+                         "frames on its replica of the world and reads them back itself (throughput; weak scaling, no "
+                         "collective on the data path); bands = ONE frame is split into row bands (latency; strong scaling). "
+                         "auto = frames where the path's frames are independent (c1, c2, c4), bands where frame k+1 depends on "
+                         "frame k (c3: temporal accumulation, c5: edit stream); an auto run at N > 1 also times the band "
+                         "split and reports it under `image_bands`")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the bounded oracle timing on rank 0")
     ap.add_argument("--no-l2-flush", action="store_true", help="do not flush L2 between timed steps")
     return ap.parse_args()
 
 
-def frame_blocks(orc, dims, n_path, count):
-    """The 192-byte RaytraceUniformData blocks of the camera path (seed = frame index + 1, pipeline.rs:201)."""
+def frame_blocks(orc, dims, n_path, count, first=0, stride=1):
+    """The 192-byte RaytraceUniformData blocks of the camera path (seed = frame index + 1, pipeline.rs:201);
+    frames first, first + stride, ... (a rank's share when the path is dealt round-robin)."""
     from raytrace_b200 import scenes
     out = []
-    for i in range(count):
+    for i in range(first, first + count * stride, stride):
         cam = scenes.camera(dims, i % n_path, n_path)
         out.append(orc.fill_frame(cam["origin"], cam["heading"], cam["pitch"], cam["sun_angle"], i + 1))
     return out
@@ -187,25 +202,25 @@ def run_reference(args, rank, world_size):
     _emit(line)
 
 
-def run_vxrt(args, rank, world_size, local_rank):
+def run_vxrt(args, rank, world_size, local_rank, shard="bands", dist=None):
+    """One measurement.  shard = "bands": one frame split into row bands over the ranks; "frames": every rank renders
+    whole frames, frame i of the path on rank i % world_size.  Returns the JSON line on rank 0 (None elsewhere)."""
     import ctypes as C
     import torch
     import raytrace_b200 as R
     from raytrace_b200 import _native as N, scenes
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; libvxrt has no CPU path (use --impl reference for the CPU baseline)")
-    dist = None
-    if world_size > 1:
-        import torch.distributed as dist
-        torch.cuda.set_device(local_rank)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    by_frames = shard == "frames" and world_size > 1
     scene, W, H, mode, n_path, accumulate, desc = WORKLOADS[args.workload]
     dims, kind, seed = scenes.WORLDS[scene]
     flags = N.FLAG_DENOISE | N.FLAG_FINALIZE | (N.FLAG_ACCUMULATE if accumulate else 0)
     noise = R.world.default_blue_noise()
     from oracle import orc                        # only the source of the seeded camera blocks, exactly as tests/ use it
     bands = [(0, H)]
-    if world_size > 1 and args.bands == "balanced":
+    if by_frames:
+        pass                                      # every rank renders whole frames
+    elif world_size > 1 and args.bands == "balanced":
         # Load-balanced bands (setup, untimed): every rank renders three frames of the path on a full-frame handle,
         # sums the per-row work counters and runs the same deterministic plan, so no rank needs to be told its rows.
         with R.Renderer(W, H, dims, mode, (flags | N.FLAG_HIT_BUFFERS) & ~N.FLAG_ACCUMULATE, device=local_rank) as cal:
@@ -217,12 +232,14 @@ def run_vxrt(args, rank, world_size, local_rank):
         bands = R.plan_bands_weighted(H, world_size, tc, dc, flags)
     elif world_size > 1:
         bands = R.plan_bands(H, world_size)
-    band = bands[rank]
-    r = R.Renderer(W, H, dims, mode, flags, device=local_rank, rows=band if world_size > 1 else None)
+    band = bands[0] if by_frames else bands[rank]
+    r = R.Renderer(W, H, dims, mode, flags, device=local_rank, rows=band if world_size > 1 and not by_frames else None)
     r.upload_blue_noise(noise)
     r.generate_world(kind, seed)                 # world replicated: every rank generates the same seeded world
     lib, h = N.lib, r.handle
-    if world_size > 1 and args.comm == "peer":
+    if by_frames:
+        pass                                      # independent replicas: nothing to attach
+    elif world_size > 1 and args.comm == "peer":
         blobs = [None] * world_size
         dist.all_gather_object(blobs, r.peer_export())       # 512-byte CUDA IPC blobs over the host channel, once
         r.peer_attach(blobs, rank, root=0)
@@ -237,7 +254,11 @@ def run_vxrt(args, rank, world_size, local_rank):
 
     # frame blocks: host-side parameter fill (pipeline.rs:191-207)
     n_frames = args.warmup + args.steps
-    blocks = frame_blocks(orc, dims, n_path, n_frames)
+    # frames mode: job-wide step k is frames k*N .. k*N+N-1 of the path, this rank renders frame k*N + rank
+    if by_frames:
+        mine_idx = R.plan_frames(n_frames * world_size, world_size)[rank]
+        assert mine_idx == list(range(rank, n_frames * world_size, world_size))
+    blocks = frame_blocks(orc, dims, n_path, n_frames, rank, world_size) if by_frames else frame_blocks(orc, dims, n_path, n_frames)
     stream = torch.cuda.ExternalStream(r.cuda_stream(), device=torch.device("cuda", local_rank))
     flush = None if args.no_l2_flush else torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local_rank}")
 
@@ -249,6 +270,8 @@ def run_vxrt(args, rank, world_size, local_rank):
 
     ne = EDITS_PER_FRAME.get(args.workload, 0)
     edits = [np.ascontiguousarray(orc.generate_edits(ne, *dims, 7, i), np.int32) for i in range(n_frames)] if ne else None
+    if ne and by_frames:
+        raise SystemExit("bench.py: the edit stream (c5) makes frame k+1 depend on frame k; use --shard bands")
     if ne and world_size > 1 and args.comm == "peer":      # edit lists travel by NCCL broadcast in either frame mode
         ident = [None]
         if rank == 0:
@@ -266,7 +289,7 @@ def run_vxrt(args, rank, world_size, local_rank):
                 r.apply_edits(edits[i])
         r.set_frame(blocks[i])
         r.render_frame()
-        if world_size > 1 and args.comm == "nccl":
+        if world_size > 1 and args.comm == "nccl" and not by_frames:
             r._check(lib.vxrt_comm_gather_output(h, 0))
 
     # ---- device-resident timing: per-step CUDA events on the handle's stream, L2 flushed between steps ----
@@ -281,7 +304,7 @@ def run_vxrt(args, rank, world_size, local_rank):
         if flush is not None:
             with torch.cuda.stream(stream):
                 flush.fill_(k & 0xFF)            # evicts L2 (126 MB) — untimed, before the step's start event
-        if world_size > 1:                       # align the ranks (untimed): a rank that starts late would otherwise
+        if world_size > 1 and not by_frames:     # align the ranks (untimed): a rank that starts late would otherwise
             if args.comm == "peer":              # put its L2 flush inside its neighbours' timed region
                 r.peer_barrier()                 # device-side barrier on the handle's stream (peer.cu)
             else:
@@ -304,8 +327,9 @@ def run_vxrt(args, rank, world_size, local_rank):
     # page-locked host images -> vxrt_wait_output of the PREVIOUS frame (the double-buffered read-back of
     # include/vxrt.h: frame k's D2H copy overlaps frame k+1's kernels).  Every frame's 8.3 MB lands in host memory
     # inside the timed region.
+    reads = rank == 0 or by_frames               # frames mode: every rank delivers the frames it rendered to host memory
     out_host = [np.empty((H, W, 4), np.uint8) for _ in range(2)]
-    if rank == 0:
+    if reads:
         for b in out_host:
             r.host_register(b)
     barrier()
@@ -313,17 +337,17 @@ def run_vxrt(args, rank, world_size, local_rank):
     prev = None
     for k in range(args.steps):
         step(args.warmup + k)
-        if rank == 0:
+        if reads:
             t = r.read_output_async(out_host[k & 1])
             if prev is not None:
                 r.wait_output(prev)
             prev = t
-    if rank == 0 and prev is not None:
+    if reads and prev is not None:
         r.wait_output(prev)
     r.sync()
     barrier()
     e2e_s = time.perf_counter() - t0
-    if rank == 0:
+    if reads:
         for b in out_host:
             r.host_unregister(b)
 
@@ -342,6 +366,8 @@ def run_vxrt(args, rank, world_size, local_rank):
     if dist is not None:
         per_rank = [None] * world_size
         dist.all_gather_object(per_rank, mine)
+    line = None
+    nf = world_size if by_frames else 1           # frames per job-wide step
     if rank == 0:
         peaks = {}
         try:
@@ -360,25 +386,27 @@ def run_vxrt(args, rank, world_size, local_rank):
         line = {
             "metric": "Mrays/s", "value": rays / (dev_ms / 1e3) / 1e6, "unit": "Mrays/s", "n_gpus": world_size,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps,
-            "frames_per_s": args.steps / (dev_ms / 1e3), "higher_is_better": True, "scaling": "strong",
+            "frames_per_s": args.steps * nf / (dev_ms / 1e3), "higher_is_better": True, "scaling": "weak" if by_frames else "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": desc, "mode": MODE_NAMES[mode], "width": W, "height": H, "world": list(dims),
-                       "passes": "trace + 6 denoise + finalize" + ("" if world_size == 1 else " + NCCL band gather (bands re-trace their halo)"
+                       "passes": "trace + 6 denoise + finalize" + ("" if world_size == 1 or by_frames else " + NCCL band gather (bands re-trace their halo)"
                                                                    if args.comm == "nccl" else
                                                                    " (halo rows pushed / bands stored into the root image over NVLink peer memory)"),
-                       "parallelism": f"image row bands x{world_size}, world replicated",
+                       "parallelism": (f"camera-path frames dealt round-robin to {world_size} GPUs (frame i on rank i % {world_size}), each renders "
+                                       f"whole frames and reads them back itself; world replicated; a step = {world_size} frames" if by_frames
+                                       else f"image row bands x{world_size}, world replicated"),
                        "bands": [list(b) for b in bands],
                        "l2": "inputs 640 MiB > L2, not flushed" if flush is None else "flushed between steps (256 MiB fill, untimed)"},
-            "rays_per_frame": rays / args.steps, "mean_steps_per_ray": steps_total / max(rays, 1.0),
+            "rays_per_frame": rays / (args.steps * nf), "mean_steps_per_ray": steps_total / max(rays, 1.0),
             "limit_exhausted": limit,
             "kernel_ms_per_step_rank0": {"trace": tot["trace_ms"] / args.steps, "denoise": tot["denoise_ms"] / args.steps,
                                           "finalize": tot["finalize_ms"] / args.steps},
             "kernel_ms_per_step_by_rank": per_rank,
             "trace_mrays_per_s_rank0": tot["rays"] / trace_s / 1e6,
-            "e2e": {"value": rays / e2e_s / 1e6, "unit": "Mrays/s", "frames_per_s": args.steps / e2e_s,
-                    "h2d_bytes_per_step": 192 + 16 * ne, "d2h_bytes_per_step": W * H * 4},
+            "e2e": {"value": rays / e2e_s / 1e6, "unit": "Mrays/s", "frames_per_s": args.steps * nf / e2e_s,
+                    "h2d_bytes_per_step": (192 + 16 * ne) * nf, "d2h_bytes_per_step": W * H * 4 * nf},
             # per frame and rank: k_trace, 6 k_denoise, k_finalize; peer mode adds k_halo_push + 3 k_peer_sync (+1 on the root)
-            "gpu_launches": args.steps * (8 * world_size + ((4 * world_size + 1) if world_size > 1 and args.comm == "peer" else 0)),
+            "gpu_launches": args.steps * (8 * world_size + ((4 * world_size + 1) if world_size > 1 and args.comm == "peer" and not by_frames else 0)),
             "roofline": {"kernel": "k_trace_fast", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
                          "algo_bytes_per_launch": tot["algo"] / args.steps, "launch_ms": tot["trace_ms"] / args.steps,
@@ -394,10 +422,8 @@ def run_vxrt(args, rank, world_size, local_rank):
                                 None if edits is None else edits[args.warmup:])
             line["cpu_baseline"] = {"value": cr / t / 1e6, "unit": "Mrays/s", "frames_per_s": nb / t, "cores": os.cpu_count(),
                                     "kind": "port", "sample": f"{nb} full frames of the same workload through the oracle (OpenMP)"}
-        _emit(line)
     r.close()
-    if dist is not None:
-        dist.destroy_process_group()
+    return line
 
 
 def _emit(line):
@@ -420,8 +446,38 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         run_reference(args, rank, world_size)
-    else:
-        run_vxrt(args, rank, world_size, local_rank)
+        return
+    dist = None
+    if world_size > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        try:                                     # run (and first-touch the page-locked frame buffers) on the GPU's own NUMA node
+            import pynvml
+            pynvml.nvmlInit()
+            pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(local_rank))
+        except Exception as e:  # noqa: BLE001
+            print(f"rank {rank}: cpu affinity not set: {e}", file=sys.stderr)
+    # frames of a camera path are independent units (c1, c2, c4): deal them to the GPUs; c3 (accumulation) and c5 (edit
+    # stream) chain frame k+1 to frame k, so only the image-space split applies
+    chained = WORKLOADS[args.workload][5] or args.workload in EDITS_PER_FRAME
+    shard = args.shard if args.shard != "auto" else ("bands" if chained else "frames")
+    line = run_vxrt(args, rank, world_size, local_rank, shard, dist)
+    if world_size > 1 and args.shard == "auto" and shard == "frames":
+        # the same workload with ONE frame split into row bands (latency of a frame instead of throughput of the path)
+        b = run_vxrt(args, rank, world_size, local_rank, "bands", dist)
+        if rank == 0:
+            line["image_bands"] = {k: b[k] for k in ("value", "unit", "ms_per_step", "frames_per_s", "scaling", "e2e", "gpu_launches",
+                                                      "kernel_ms_per_step_by_rank")}
+            line["image_bands"]["parallelism"] = b["config"]["parallelism"]
+            line["image_bands"]["bands"] = b["config"]["bands"]
+            line["image_bands"]["passes"] = b["config"]["passes"]
+            line["gpu_launches"] += b["gpu_launches"]
+    if rank == 0:
+        _emit(line)
+    if dist is not None:
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

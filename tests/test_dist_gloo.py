@@ -25,6 +25,7 @@ def _worker(rank, world_size, port, q):
         dims, kind, seed = scenes.WORLDS["c1"]
         m, f = orc.build_minefield(orc.generate_world(*dims, kind, seed))      # replicated world
         noise = orc.blue_noise()
+        m_path, f_path = m.copy(), f.copy()        # the world before the edit broadcast below
         W, H = 96, 320
         cam = scenes.camera(dims)
         blk = orc.fill_frame(cam["origin"], cam["heading"], cam["pitch"], cam["sun_angle"], 4)
@@ -65,7 +66,22 @@ def _worker(rank, world_size, port, q):
         both = [torch.zeros_like(digest) for _ in range(world_size)]
         dist.all_gather(both, digest)
         ok_world = all(bool(torch.equal(both[0], x)) for x in both)
-        q.put((rank, ok_img, ok_world))
+        # frames of a camera path dealt round-robin (plan_frames): the ranks' frames together are the path, in order
+        n_path = 5
+        mine_idx = R.plan_frames(n_path, world_size)[rank]
+        sums = torch.zeros(n_path, dtype=torch.int64)
+        for i in mine_idx:
+            c = scenes.camera(dims, i, n_path)
+            bi = orc.fill_frame(c["origin"], c["heading"], c["pitch"], c["sun_angle"], i + 1)
+            sums[i] = int(orc.render(m_path, f_path, noise, bi, 1, 64, 40, denoise=True, finalize=True).output.astype(np.int64).sum())
+        dist.all_reduce(sums)
+        ok_frames = True
+        if rank == 0:
+            for i in range(n_path):
+                c = scenes.camera(dims, i, n_path)
+                bi = orc.fill_frame(c["origin"], c["heading"], c["pitch"], c["sun_angle"], i + 1)
+                ok_frames &= int(orc.render(m_path, f_path, noise, bi, 1, 64, 40, denoise=True, finalize=True).output.astype(np.int64).sum()) == int(sums[i])
+        q.put((rank, ok_img, ok_world and ok_frames))
     finally:
         dist.destroy_process_group()
 
