@@ -63,6 +63,7 @@ class VxrtFrameStats(C.Structure):
 _H = C.c_void_p
 SYMBOLS = {
     "vxrt_create": (C.c_int, [C.POINTER(VxrtConfig), C.POINTER(_H)]),
+    "vxrt_create_shared": (C.c_int, [C.POINTER(VxrtConfig), _H, C.POINTER(_H)]),
     "vxrt_destroy": (None, [_H]),
     "vxrt_last_error": (C.c_char_p, [_H]),
     "vxrt_abi_version": (C.c_int, []),

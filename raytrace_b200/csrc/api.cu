@@ -157,6 +157,21 @@ int mark_dirty_box(VxrtHandle* h, int x0, int y0, int z0, int ex, int ey, int ez
     return VXRT_OK;
 }
 
+// World writes on a handle whose world other handles borrow (vxrt_create_shared): the borrowers' frames in flight
+// finish first; their next frame waits for the write (ev_world) on its own stream.
+int world_write_begin(VxrtHandle* h, const char* who) {
+    if (h->world_owner) { h->err = std::string(who) + ": this handle borrows its world (vxrt_create_shared); write through the owner"; return VXRT_ERR_STATE; }
+    for (VxrtHandle* s : h->sharers) CU(cudaStreamSynchronize(s->stream));
+    return VXRT_OK;
+}
+int world_write_end(VxrtHandle* h) {
+    if (h->sharers.empty()) return VXRT_OK;
+    CU(cudaEventRecord(h->ev_world, h->stream));
+    h->world_version++;
+    return VXRT_OK;
+}
+const VxrtHandle* world_of(const VxrtHandle* h) { return h->world_owner ? h->world_owner : h; }
+
 int rebuild_dirty(VxrtHandle* h) {
     CU(vxrt_launch_build_minefield(h->d_materials, h->d_minefield, h->cfg.nx, h->cfg.ny, h->cfg.nz, h->d_dirty, h->stream));
     CU(cudaMemsetAsync(h->d_dirty, 0, (size_t)(h->cfg.nx >> 6) * (h->cfg.ny >> 6) * (h->cfg.nz >> 6) * 4, h->stream));
@@ -252,7 +267,7 @@ int vxrt_plan_bands_weighted(int height, int nranks, uint32_t flags, const float
 
 const char* vxrt_last_error(const VxrtHandle* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
 
-int vxrt_create(const VxrtConfig* cfg, VxrtHandle** out) {
+static int create_impl(const VxrtConfig* cfg, VxrtHandle* owner, VxrtHandle** out) {
     if (!out) { g_create_error = "vxrt_create: out is NULL"; return VXRT_ERR_INVALID; }
     *out = nullptr;
     if (!cfg) { g_create_error = "vxrt_create: cfg is NULL"; return VXRT_ERR_INVALID; }
@@ -280,6 +295,12 @@ int vxrt_create(const VxrtConfig* cfg, VxrtHandle** out) {
         return VXRT_ERR_CUDA;
     }
     if (cfg->device < 0 || cfg->device >= ndev) { g_create_error = "vxrt_create: device ordinal out of range"; return VXRT_ERR_INVALID; }
+    if (owner) {
+        if (owner->world_owner) { g_create_error = "vxrt_create_shared: the owner itself borrows its world"; return VXRT_ERR_INVALID; }
+        if (owner->cfg.device != cfg->device || owner->cfg.nx != cfg->nx || owner->cfg.ny != cfg->ny || owner->cfg.nz != cfg->nz) {
+            g_create_error = "vxrt_create_shared: device and window dims must equal the owner's"; return VXRT_ERR_INVALID;
+        }
+    }
     e = cudaSetDevice(cfg->device);
     if (e != cudaSuccess) { g_create_error = std::string("cudaSetDevice: ") + cudaGetErrorString(e); return VXRT_ERR_CUDA; }
 
@@ -319,10 +340,15 @@ int vxrt_create(const VxrtConfig* cfg, VxrtHandle** out) {
         }
         const size_t V = voxels(h), P = pixels(h);
         int rc;
-        if ((rc = alloc_zero(h, (void**)&h->d_materials, V * 4))) return rc;
-        if ((rc = alloc_zero(h, (void**)&h->d_minefield, V))) return rc;
-        if ((rc = alloc_zero(h, (void**)&h->d_noise, h->h_noise.size()))) return rc;
-        if ((rc = alloc_zero(h, (void**)&h->d_dirty, (size_t)(cfg->nx >> 6) * (cfg->ny >> 6) * (cfg->nz >> 6) * 4))) return rc;
+        CU(cudaEventCreateWithFlags(&h->ev_world, cudaEventDisableTiming));
+        if (owner) {                             // the world is the owner's: no second copy in HBM
+            h->d_materials = owner->d_materials; h->d_minefield = owner->d_minefield; h->d_noise = owner->d_noise;
+        } else {
+            if ((rc = alloc_zero(h, (void**)&h->d_materials, V * 4))) return rc;
+            if ((rc = alloc_zero(h, (void**)&h->d_minefield, V))) return rc;
+            if ((rc = alloc_zero(h, (void**)&h->d_noise, h->h_noise.size()))) return rc;
+            if ((rc = alloc_zero(h, (void**)&h->d_dirty, (size_t)(cfg->nx >> 6) * (cfg->ny >> 6) * (cfg->nz >> 6) * 4))) return rc;
+        }
         if ((rc = alloc_zero(h, (void**)&h->d_counters, 8 * sizeof(unsigned long long)))) return rc;
         std::vector<float> lut((size_t)VXRT_LUT_SCREEN + cfg->width + cfg->height);
         CU(cudaMalloc((void**)&h->d_lut, lut.size() * sizeof(float)));
@@ -361,9 +387,22 @@ int vxrt_create(const VxrtConfig* cfg, VxrtHandle** out) {
         return VXRT_OK;
     };
     const int rc = init();
-    if (rc != VXRT_OK) { g_create_error = h->err; vxrt_destroy(h); return rc; }
+    if (rc != VXRT_OK) {
+        if (owner) h->d_materials = nullptr, h->d_minefield = nullptr, h->d_noise = nullptr;
+        g_create_error = h->err; vxrt_destroy(h); return rc;
+    }
+    if (owner) { h->world_owner = owner; owner->sharers.push_back(h); h->world_seen = owner->world_version; }
     *out = h;
     return VXRT_OK;
+}
+
+int vxrt_create(const VxrtConfig* cfg, VxrtHandle** out) { return create_impl(cfg, nullptr, out); }
+
+int vxrt_create_shared(const VxrtConfig* cfg, VxrtHandle* owner, VxrtHandle** out) {
+    if (!owner) { g_create_error = "vxrt_create_shared: owner is NULL"; if (out) *out = nullptr; return VXRT_ERR_INVALID; }
+    cudaSetDevice(owner->cfg.device);
+    cudaStreamSynchronize(owner->stream);        // whatever the owner has uploaded so far is visible to the new handle
+    return create_impl(cfg, owner, out);
 }
 
 void vxrt_destroy(VxrtHandle* h) {
@@ -373,6 +412,17 @@ void vxrt_destroy(VxrtHandle* h) {
     if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
     vxrt_comm_release(h);
     vxrt_peer_release(h);
+    if (h->world_owner) {                        // borrowed world: unregister, free nothing of it
+        auto& v = h->world_owner->sharers;
+        for (size_t i = 0; i < v.size(); i++) if (v[i] == h) { v.erase(v.begin() + i); break; }
+        h->d_materials = nullptr; h->d_minefield = nullptr; h->d_noise = nullptr;
+    }
+    for (VxrtHandle* s : h->sharers) {           // an owner destroyed first leaves its borrowers without a world
+        cudaStreamSynchronize(s->stream);
+        s->world_owner = nullptr; s->d_materials = nullptr; s->d_minefield = nullptr; s->d_noise = nullptr;
+        s->have_world = s->have_noise = false;
+    }
+    if (h->ev_world) cudaEventDestroy(h->ev_world);
     void* ptrs[] = {h->d_materials, h->d_minefield, h->d_noise, h->d_lut, h->d_dirty, h->d_edits, h->d_lighting, h->d_pong,
                     h->d_lighting_raw, h->d_depth, h->d_normal, h->d_albedo, h->d_emission, h->d_fog, h->d_out_buf[0], h->d_out_buf[1],
                     h->d_hit_voxel, h->d_hit_face, h->d_hit_word, h->d_hit_t, h->d_steps, h->d_rays, h->d_accum, h->d_counters,
@@ -396,6 +446,7 @@ int vxrt_upload_chunk(VxrtHandle* h, int cx, int cy, int cz, const uint32_t* mat
     if (cx < 0 || cy < 0 || cz < 0 || cx >= (h->cfg.nx >> 6) || cy >= (h->cfg.ny >> 6) || cz >= (h->cfg.nz >> 6))
         return fail(h, VXRT_ERR_INVALID, "vxrt_upload_chunk: chunk coordinate outside the window");
     CU(cudaSetDevice(h->cfg.device));
+    { const int wrc = world_write_begin(h, "vxrt_upload_chunk"); if (wrc) return wrc; }
     int rc;
     if ((rc = upload_box(h, h->d_materials, materials, cx * 64, cy * 64, cz * 64, 64, 64, 64))) return rc;
     if (minefield) {
@@ -406,20 +457,21 @@ int vxrt_upload_chunk(VxrtHandle* h, int cx, int cy, int cz, const uint32_t* mat
     }
     CU(cudaStreamSynchronize(h->stream));     // caller may free its buffers on return
     h->have_world = true;
-    return VXRT_OK;
+    return world_write_end(h);
 }
 
 int vxrt_upload_world(VxrtHandle* h, const uint32_t* materials, const uint8_t* minefield) {
     if (!h) return VXRT_ERR_INVALID;
     if (!materials) return fail(h, VXRT_ERR_INVALID, "vxrt_upload_world: materials is NULL");
     CU(cudaSetDevice(h->cfg.device));
+    { const int wrc = world_write_begin(h, "vxrt_upload_world"); if (wrc) return wrc; }
     const size_t V = voxels(h);
     CU(cudaMemcpyAsync(h->d_materials, materials, V * 4, cudaMemcpyHostToDevice, h->stream));
     if (minefield) CU(cudaMemcpyAsync(h->d_minefield, minefield, V, cudaMemcpyHostToDevice, h->stream));
     else CU(vxrt_launch_build_minefield(h->d_materials, h->d_minefield, h->cfg.nx, h->cfg.ny, h->cfg.nz, nullptr, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     h->have_world = true;
-    return VXRT_OK;
+    return world_write_end(h);
 }
 
 int vxrt_upload_slice(VxrtHandle* h, int axis, int offset, const uint32_t* materials, const uint8_t* minefield) {
@@ -432,6 +484,7 @@ int vxrt_upload_slice(VxrtHandle* h, int axis, int offset, const uint32_t* mater
     int e[3] = {dims[0], dims[1], dims[2]}, o[3] = {0, 0, 0};
     e[axis] = 16; o[axis] = offset;                           // constants.rs:30 SLICE_SIZE
     CU(cudaSetDevice(h->cfg.device));
+    { const int wrc = world_write_begin(h, "vxrt_upload_slice"); if (wrc) return wrc; }
     int rc;
     if ((rc = upload_box(h, h->d_materials, materials, o[0], o[1], o[2], e[0], e[1], e[2]))) return rc;
     if (minefield) {
@@ -442,30 +495,33 @@ int vxrt_upload_slice(VxrtHandle* h, int axis, int offset, const uint32_t* mater
     }
     CU(cudaStreamSynchronize(h->stream));
     h->have_world = true;
-    return VXRT_OK;
+    return world_write_end(h);
 }
 
 int vxrt_generate_world(VxrtHandle* h, int kind, uint32_t seed) {
     if (!h) return VXRT_ERR_INVALID;
     if (kind < 0 || kind > 1) return fail(h, VXRT_ERR_INVALID, "vxrt_generate_world: kind must be 0 (heightmap) or 1 (biome)");
     CU(cudaSetDevice(h->cfg.device));
+    { const int wrc = world_write_begin(h, "vxrt_generate_world"); if (wrc) return wrc; }
     CU(vxrt_launch_generate(h->d_materials, h->cfg.nx, h->cfg.ny, h->cfg.nz, kind, seed, h->stream));
     CU(vxrt_launch_build_minefield(h->d_materials, h->d_minefield, h->cfg.nx, h->cfg.ny, h->cfg.nz, nullptr, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     h->have_world = true;
-    return VXRT_OK;
+    return world_write_end(h);
 }
 
 int vxrt_rebuild_minefield(VxrtHandle* h) {
     if (!h) return VXRT_ERR_INVALID;
     CU(cudaSetDevice(h->cfg.device));
+    { const int wrc = world_write_begin(h, "vxrt_rebuild_minefield"); if (wrc) return wrc; }
     CU(vxrt_launch_build_minefield(h->d_materials, h->d_minefield, h->cfg.nx, h->cfg.ny, h->cfg.nz, nullptr, h->stream));
     CU(cudaStreamSynchronize(h->stream));
-    return VXRT_OK;
+    return world_write_end(h);
 }
 
 int vxrt_read_world(VxrtHandle* h, uint32_t* materials, uint8_t* minefield) {
     if (!h) return VXRT_ERR_INVALID;
+    if (h->world_owner) return fail(h, VXRT_ERR_STATE, "vxrt_read_world: this handle borrows its world (vxrt_create_shared); read through the owner");
     CU(cudaSetDevice(h->cfg.device));
     const size_t V = voxels(h);
     if (materials) CU(cudaMemcpyAsync(materials, h->d_materials, V * 4, cudaMemcpyDeviceToHost, h->stream));
@@ -479,11 +535,12 @@ int vxrt_upload_blue_noise(VxrtHandle* h, const uint8_t* rgba, size_t nbytes) {
     if (!rgba) return fail(h, VXRT_ERR_INVALID, "vxrt_upload_blue_noise: rgba is NULL");
     if (nbytes != h->h_noise.size()) return fail(h, VXRT_ERR_SIZE, "vxrt_upload_blue_noise: expected 512*512*4 bytes");
     CU(cudaSetDevice(h->cfg.device));
+    { const int wrc = world_write_begin(h, "vxrt_upload_blue_noise"); if (wrc) return wrc; }
     memcpy(h->h_noise.data(), rgba, nbytes);
     CU(cudaMemcpyAsync(h->d_noise, h->h_noise.data(), nbytes, cudaMemcpyHostToDevice, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     h->have_noise = true;
-    return VXRT_OK;
+    return world_write_end(h);
 }
 
 // ---- edits ------------------------------------------------------------------------------------
@@ -491,16 +548,20 @@ int vxrt_upload_blue_noise(VxrtHandle* h, const uint8_t* rgba, size_t nbytes) {
 int vxrt_apply_edits_device(VxrtHandle* h, const void* d_edits, size_t n) {
     if (!h) return VXRT_ERR_INVALID;
     if (n && !d_edits) return fail(h, VXRT_ERR_INVALID, "vxrt_apply_edits_device: d_edits is NULL");
+    if (h->world_owner) return fail(h, VXRT_ERR_STATE, "vxrt_apply_edits_device: this handle borrows its world (vxrt_create_shared); write through the owner");
     if (!h->have_world) return fail(h, VXRT_ERR_STATE, "vxrt_apply_edits: no world uploaded");
     if (n == 0) return VXRT_OK;
     CU(cudaSetDevice(h->cfg.device));
+    { const int wrc = world_write_begin(h, "vxrt_apply_edits_device"); if (wrc) return wrc; }
     CU(vxrt_launch_apply_edits(h->d_materials, h->d_dirty, (const VxrtEdit*)d_edits, n, h->cfg.nx, h->cfg.ny, h->cfg.nz, h->stream));
-    return rebuild_dirty(h);
+    { const int rc = rebuild_dirty(h); if (rc) return rc; }
+    return world_write_end(h);
 }
 
 int vxrt_apply_edits(VxrtHandle* h, const VxrtEdit* edits, size_t n) {
     if (!h) return VXRT_ERR_INVALID;
     if (n && !edits) return fail(h, VXRT_ERR_INVALID, "vxrt_apply_edits: edits is NULL");
+    if (h->world_owner) return fail(h, VXRT_ERR_STATE, "vxrt_apply_edits: this handle borrows its world (vxrt_create_shared); write through the owner");
     if (!h->have_world) return fail(h, VXRT_ERR_STATE, "vxrt_apply_edits: no world uploaded");
     if (n == 0) return VXRT_OK;
     CU(cudaSetDevice(h->cfg.device));
@@ -551,8 +612,9 @@ int vxrt_reset_history(VxrtHandle* h) {
 
 int vxrt_render_frame(VxrtHandle* h) {
     if (!h) return VXRT_ERR_INVALID;
-    if (!h->have_world) return fail(h, VXRT_ERR_STATE, "vxrt_render_frame: no world uploaded");
-    if (!h->have_noise) return fail(h, VXRT_ERR_STATE, "vxrt_render_frame: no blue noise uploaded");
+    const VxrtHandle* wo = world_of(h);
+    if (!wo->have_world) return fail(h, VXRT_ERR_STATE, "vxrt_render_frame: no world uploaded");
+    if (!wo->have_noise) return fail(h, VXRT_ERR_STATE, "vxrt_render_frame: no blue noise uploaded");
     if (!h->have_frame) return fail(h, VXRT_ERR_STATE, "vxrt_render_frame: vxrt_set_frame not called");
     CU(cudaSetDevice(h->cfg.device));
     const VxrtFrameParams& f = h->frame;
@@ -576,7 +638,7 @@ int vxrt_render_frame(VxrtHandle* h) {
     {   // raytrace.comp:298-303: texel (seed % 512, seed / 512), clamp-to-edge (render_data.rs:110-128)
         uint32_t ix = f.seed % VXRT_NOISE_SIZE, iy = f.seed / VXRT_NOISE_SIZE;
         if (iy > VXRT_NOISE_SIZE - 1) iy = VXRT_NOISE_SIZE - 1;
-        const uint8_t* t = h->h_noise.data() + ((size_t)iy * VXRT_NOISE_SIZE + ix) * 4;
+        const uint8_t* t = wo->h_noise.data() + ((size_t)iy * VXRT_NOISE_SIZE + ix) * 4;
         P.noise_base_x = ((float)t[0] / 255.0f) * 255.0f;
         P.noise_base_y = ((float)t[1] / 255.0f) * 255.0f;
     }
@@ -611,6 +673,10 @@ int vxrt_render_frame(VxrtHandle* h) {
     h->d_output = h->d_out_buf[h->out_idx];
     int prc;
     if (h->peer_on && (prc = vxrt_peer_begin_frame(h, h->out_idx))) return prc;
+    if (h->world_owner && h->world_seen != h->world_owner->world_version) {    // the owner wrote its world since this handle's last frame
+        CU(cudaStreamWaitEvent(h->stream, h->world_owner->ev_world, 0));
+        h->world_seen = h->world_owner->world_version;
+    }
     CU(cudaMemsetAsync(h->d_counters, 0, 8 * sizeof(unsigned long long), h->stream));
     CU(cudaEventRecord(h->ev[0], h->stream));
     if (!h->peer_on) {

@@ -74,7 +74,10 @@ struct VxrtHandle {
     cudaStream_t copy_stream; cudaEvent_t ev_frame_done[2], ev_copy_done[2]; bool copy_pending[2];
     uchar4* d_out_buf[2]; int out_idx; unsigned long long tickets, ticket_of_buf[2];
     std::string err;
-    // world
+    // world.  A handle made by vxrt_create_shared borrows d_materials / d_minefield / d_noise from world_owner (same
+    // device) and never writes them; the owner orders its world writes against the borrowers' frames (api.cu world_write_*)
+    VxrtHandle* world_owner = nullptr; std::vector<VxrtHandle*> sharers;
+    cudaEvent_t ev_world = nullptr; unsigned long long world_version = 0, world_seen = 0;
     uint32_t* d_materials; uint8_t* d_minefield; uint8_t* d_noise; float* d_lut;
     std::vector<uint8_t> h_noise;        // host copy: the seed texel is read on the host (raytrace.comp:298-303)
     uint32_t* d_dirty;                   // one flag per 64^3 chunk

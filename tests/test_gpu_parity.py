@@ -491,3 +491,48 @@ def test_refined_division_is_ieee_division():
         bad = C.c_uint64(123)
         assert lib.vxrt_selftest_division(0, 1 << 27, seed, C.byref(bad)) == N.OK
         assert bad.value == 0
+
+
+def test_shared_world_handles_and_frames_in_flight(orc, world, noise):
+    """vxrt_create_shared: a borrower renders from the owner's world (no second copy) on its own stream; frames
+    submitted alternately (FramePipeline) equal the frames of a standalone handle bit for bit; world writes go through
+    the owner and reach the borrower's next frame; a borrower rejects them."""
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    dims = scenes.WORLDS["mid"][0]
+    m, f = world("mid")
+    W, H = 200, 120
+    flags = N.FLAG_HIT_BUFFERS | N.FLAG_DENOISE | N.FLAG_FINALIZE
+    blocks = [_frame_block(orc, dims, k, 6, seed=20 + k) for k in range(6)]
+    with R.Renderer(W, H, dims, N.MODE_FULL, flags) as solo:
+        solo.upload_blue_noise(noise); solo.upload_world(m, f)
+        want = []
+        for b in blocks:
+            solo.set_frame(b); solo.render_frame()
+            want.append((solo.read_output().copy(), solo.read_buffer(N.BUF_HIT_VOXEL).copy(), solo.frame_stats().steps))
+        edits = orc.generate_edits(2000, *dims, 7, 0)
+        solo.apply_edits(edits)
+        solo.set_frame(blocks[0]); solo.render_frame()
+        want_edit = solo.read_output().copy()
+    with R.FramePipeline(W, H, dims, N.MODE_FULL, flags, depth=3) as fp:
+        fp.owner.upload_blue_noise(noise); fp.owner.upload_world(m, f)
+        used = [fp.submit(b) for b in blocks[:3]]                      # three frames in flight, one per handle
+        for r, (img, vox, steps) in zip(used, want[:3]):
+            assert np.array_equal(r.read_output(), img) and np.array_equal(r.read_buffer(N.BUF_HIT_VOXEL), vox)
+            assert r.frame_stats().steps == steps
+        used = [fp.submit(b) for b in blocks[3:]]
+        for r, (img, vox, steps) in zip(used, want[3:]):
+            assert np.array_equal(r.read_output(), img)
+        borrower = fp.renderers[1]
+        with pytest.raises(R.VxrtError) as e:
+            borrower.apply_edits(edits)
+        assert e.value.code == N.ERR_STATE
+        with pytest.raises(R.VxrtError):
+            borrower.generate_world(0, 1)
+        fp.owner.apply_edits(edits)                                   # ordered against the borrowers' frames
+        borrower.set_frame(blocks[0]); borrower.render_frame()
+        assert np.array_equal(borrower.read_output(), want_edit)
+    # a handle on another window cannot borrow
+    with R.Renderer(64, 64, (64, 64, 64)) as a:
+        with pytest.raises(R.VxrtError):
+            R.Renderer(64, 64, (128, 64, 64), share_world=a)
