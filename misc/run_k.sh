@@ -1,0 +1,19 @@
+#!/bin/bash
+# denoise accumulation variants (VXRT_DN_PACK) A/B on one box, then the GPU tests on the default build
+mkdir -p gpurun_out
+for v in dn0 dn1 dn3 dn3l4; do
+  for w in c2 c3; do
+    VXRT_LIB=$PWD/raytrace_b200/libvxrt_$v.so timeout 300 python bench.py --no-cpu-baseline --workload $w --steps 32 > gpurun_out/k_${w}_$v.json 2>gpurun_out/k_${w}_$v.err || tail -5 gpurun_out/k_${w}_$v.err
+  done
+done
+timeout 300 python bench.py --no-cpu-baseline --in-flight 3 --steps 32 > gpurun_out/k_c2_s3.json 2>gpurun_out/k_c2_s3.err
+python - <<PY
+import json
+for v in ("dn0","dn1","dn3","dn3l4","s3"):
+  for w in ("c2","c3"):
+    try:
+        d=json.load(open("gpurun_out/k_%s_%s.json"%(w,v))); o=d["one_frame_in_flight"]; k=d["kernel_ms_per_step_rank0"]
+        print(v,w,"S=%d fps=%.0f ms=%.4f | serial ms=%.4f | trace %.4f denoise %.4f fin %.4f | e2e fps=%.0f"%(d["config"]["frames_in_flight"],d["frames_per_s"],d["ms_per_step"],o["ms_per_step"],k["trace"],k["denoise"],k["finalize"],d["e2e"]["frames_per_s"]))
+    except Exception as e: print(v,w,"failed",e)
+PY
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -15 > gpurun_out/k_pytest.txt; tail -5 gpurun_out/k_pytest.txt

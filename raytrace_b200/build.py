@@ -36,6 +36,14 @@ def needs_build():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
+def build_variant(tag, extra):
+    """libvxrt_<tag>.so with extra nvcc flags (kernel-variant A/B runs; picked up through VXRT_LIB)."""
+    out = os.path.join(HERE, f"libvxrt_{tag}.so")
+    srcs = [os.path.join(CSRC, s) for s in SOURCES]
+    subprocess.run([_nvcc()] + NVCC_FLAGS + list(extra) + ["-o", out] + srcs + ["-ldl"], cwd=CSRC, check=True)
+    return out
+
+
 def build(force=False, verbose=False):
     srcs = [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
     if not force and not needs_build():
@@ -64,6 +72,10 @@ def build_host(verbose=False):
     return HOST_OUT
 
 
+if __name__ == "__main__" and "--variant" in sys.argv:
+    i = sys.argv.index("--variant")
+    print(build_variant(sys.argv[i + 1], sys.argv[i + 2:]))
+    sys.exit(0)
 if __name__ == "__main__":
     build(force="--force" in sys.argv, verbose="--verbose" in sys.argv)
     print(OUT)

@@ -39,6 +39,16 @@ __device__ __forceinline__ uint32_t lds_u16(const uint16_t* p) {
     asm volatile("ld.shared.u16 %0, [%1];" : "=r"(r) : "r"((uint32_t)__cvta_generic_to_shared(p)));
     return r;
 }
+// Packed fp32 accumulation (sm_100a FFMA2 = fma.rn.f32x2, one issue slot for two lanes): VXRT_DN_PACK 1 packs the
+// (r, g) sums, 2 also packs (b, weight sum) against a per-texel {b, 1.0} pair.  The kernel is issue-bound, so the
+// slots are what counts (the FMA pipe is busy the same number of cycles either way, misc/ubench/f32x2.cu).
+#ifndef VXRT_DN_PACK
+#define VXRT_DN_PACK 3
+#endif
+typedef unsigned long long dn_f2;
+__device__ __forceinline__ dn_f2 dn_pk(float lo, float hi) { dn_f2 r; asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void dn_unpk(dn_f2 v, float& lo, float& hi) { asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ dn_f2 dn_fma2(dn_f2 a, dn_f2 b, dn_f2 c) { dn_f2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
 constexpr int DN_TX = 128;                     // pixels per CTA row
 #ifndef VXRT_DN_TY
 #define VXRT_DN_TY 2
@@ -61,7 +71,8 @@ constexpr int DN_UNROLL = VXRT_DN_UNROLL;      // staging loop unroll (global lo
 #endif
 template <int S, int L> struct DnTile {
     static constexpr int W = DN_TX + 6 * S, R = L + 6, N = W * R;
-    static constexpr size_t BYTES = (size_t)N * (sizeof(float4) + sizeof(uint16_t));
+    // PACK 3: texel = {r, g, b, 1.0} + {dist, normal code} (24 B) so (b, 1.0) is a register pair straight from LDS.128
+    static constexpr size_t BYTES = (size_t)N * (sizeof(float4) + (VXRT_DN_PACK == 3 ? sizeof(float2) : sizeof(uint16_t)));
 };
 // SAMPLE list of bilateral_denoise.comp:43-86 as a function of (|dx|, |dy|); 0 = not a tap
 __host__ __device__ constexpr float dn_weight(int ax, int ay) {
@@ -79,6 +90,7 @@ __global__ void __launch_bounds__(DN_TX * DN_TY, VXRT_DN_MINB) k_denoise(const u
     using T = DnTile<S, L>;
     extern __shared__ float4 dn_tile[];
     uint16_t* dn_nrm = reinterpret_cast<uint16_t*>(dn_tile + T::N);
+    float2* dn_aux = reinterpret_cast<float2*>(dn_tile + T::N);       // VXRT_DN_PACK == 3
     const int tid = threadIdx.y * DN_TX + threadIdx.x;
     const int bx = blockIdx.x * DN_TX;
     const int res = blockIdx.y / groups, grp = blockIdx.y - res * groups;   // y-residue class, group of L decimated rows
@@ -115,8 +127,13 @@ __global__ void __launch_bounds__(DN_TX * DN_TY, VXRT_DN_MINB) k_denoise(const u
         const ushort4 q = __ldg(src + gi);
         const uint32_t d = __ldg(depth + gi), n = __ldg(normal + gi);
         const float k = 1.0f / 65535.0f;
+#if VXRT_DN_PACK == 3
+        dn_tile[e] = make_float4((float)q.x * k, (float)q.y * k, (float)q.z * k, 1.0f);
+        dn_aux[e] = make_float2((float)(SWAP ? n : d) * (1.0f / 256.0f), __uint_as_float(SWAP ? d : n));   // :37
+#else
         dn_tile[e] = make_float4((float)q.x * k, (float)q.y * k, (float)q.z * k, (float)(SWAP ? n : d) * (1.0f / 256.0f));   // :37
         dn_nrm[e] = (uint16_t)(SWAP ? d : n);
+#endif
     }
     __syncthreads();
     if (x >= width) return;
@@ -125,12 +142,18 @@ __global__ void __launch_bounds__(DN_TX * DN_TY, VXRT_DN_MINB) k_denoise(const u
     for (int o0 = threadIdx.y * DN_G; o0 < L; o0 += DN_TY * DN_G) {       // outputs o0 .. o0+G-1 (decimated rows)
         if (ybase + o0 * S >= row1) break;
         float tw[DN_G], sr[DN_G], sg[DN_G], sb[DN_G], cd[DN_G];
+        dn_f2 srg[DN_G], sbw[DN_G];                        // VXRT_DN_PACK: (r, g) and (b, weight) sums as f32x2 pairs
         uint32_t cn[DN_G];
 #pragma unroll
         for (int k = 0; k < DN_G; k++) {                   // centre of output k is staged row o0 + k + 3
+#if VXRT_DN_PACK == 3
+            { const float2 a = dn_aux[(o0 + k + 3) * T::W + c0]; cd[k] = a.x; cn[k] = __float_as_uint(a.y); }
+#else
             cd[k] = dn_tile[(o0 + k + 3) * T::W + c0].w;
             cn[k] = lds_u16(dn_nrm + (o0 + k + 3) * T::W + c0);
+#endif
             tw[k] = 0.0f; sr[k] = 0.0f; sg[k] = 0.0f; sb[k] = 0.0f;
+            srg[k] = dn_pk(0.0f, 0.0f); sbw[k] = dn_pk(0.0f, 0.0f);
         }
         bool sky = true;
 #pragma unroll
@@ -157,7 +180,15 @@ __global__ void __launch_bounds__(DN_TX * DN_TY, VXRT_DN_MINB) k_denoise(const u
             for (int dx = -3; dx <= 3; dx++) {
                 if (dx < -wmax || dx > wmax) continue;
                 const float4 t = dn_tile[(o0 + rho) * T::W + c0 + dx * S];
+#if VXRT_DN_PACK == 3
+                const float2 ta = dn_aux[(o0 + rho) * T::W + c0 + dx * S];
+                const float td = ta.x; const uint32_t tn = __float_as_uint(ta.y);
+                const dn_f2 trg = dn_pk(t.x, t.y), tb1 = dn_pk(t.z, t.w);
+#else
                 const uint32_t tn = lds_u16(dn_nrm + (o0 + rho) * T::W + c0 + dx * S);
+                const float td = t.w;
+                const dn_f2 trg = dn_pk(t.x, t.y), tb1 = dn_pk(t.z, 1.0f);
+#endif
 #pragma unroll
                 for (int k = 0; k < DN_G; k++) {
                     const int dy = rho - 3 - k;
@@ -170,9 +201,16 @@ __global__ void __launch_bounds__(DN_TX * DN_TY, VXRT_DN_MINB) k_denoise(const u
                     } else {
                         // w = wgt / (4|dc - dq| + (nq == nc ? 0 : 10) + 1)   (:23-33), one reciprocal of the scaled sum
                         const float pen = (tn == cn[k]) ? (1.0f / wgt) : (11.0f / wgt);
-                        w = rcp_fast(fmaf(4.0f / wgt, fabsf(cd[k] - t.w), pen));
+                        w = rcp_fast(fmaf(4.0f / wgt, fabsf(cd[k] - td), pen));
                     }
+#if VXRT_DN_PACK >= 2
+                    const dn_f2 ww = dn_pk(w, w);
+                    srg[k] = dn_fma2(trg, ww, srg[k]); sbw[k] = dn_fma2(tb1, ww, sbw[k]);
+#elif VXRT_DN_PACK == 1
+                    tw[k] += w; srg[k] = dn_fma2(trg, dn_pk(w, w), srg[k]); sb[k] = fmaf(t.z, w, sb[k]);
+#else
                     tw[k] += w; sr[k] = fmaf(t.x, w, sr[k]); sg[k] = fmaf(t.y, w, sg[k]); sb[k] = fmaf(t.z, w, sb[k]);
+#endif
                 }
             }
         }
@@ -181,6 +219,12 @@ __global__ void __launch_bounds__(DN_TX * DN_TY, VXRT_DN_MINB) k_denoise(const u
             const int y = ybase + (o0 + k) * S;
             if (y >= row1) break;
             const size_t pi = (size_t)y * width + x;
+#if VXRT_DN_PACK >= 1
+            dn_unpk(srg[k], sr[k], sg[k]);
+#endif
+#if VXRT_DN_PACK >= 2
+            dn_unpk(sbw[k], sb[k], tw[k]);
+#endif
             if (cn[k] >= 16) {
                 dst[pi] = __ldg(src + pi);                                     // :88-89
             } else {
