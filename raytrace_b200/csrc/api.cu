@@ -720,12 +720,15 @@ int vxrt_render_frame(VxrtHandle* h) {
     if (h->cfg.flags & VXRT_FLAG_DENOISE) {
         // pipeline.rs:98-115: even passes lighting -> pong, odd passes pong -> lighting.  A band shrinks
         // by 3*size rows per pass towards [row0,row1) so that only valid rows are ever read.
+        // passes 2..6 follow a denoise launch directly: programmatic dependent launch (post.cu) lets a pass become
+        // resident while its predecessor drains
+        static const bool pdl = getenv("VXRT_NO_PDL") == nullptr;
         for (int k = 0; k < 6; k++) {
             const int r0 = h->plan[2 + 2 * k], r1 = h->plan[3 + 2 * k];
             const bool odd = (k & 1) != 0;
             const int swap = (odd && (h->cfg.flags & VXRT_FLAG_PONG_SWAP)) ? 1 : 0;
             CU(vxrt_launch_denoise(odd ? h->d_pong : h->d_lighting, odd ? h->d_lighting : h->d_pong, h->d_depth, h->d_normal,
-                                   h->cfg.width, h->cfg.height, kDenoiseSizes[k], swap, r0, r1, h->stream));
+                                   h->cfg.width, h->cfg.height, kDenoiseSizes[k], swap, r0, r1, h->stream, k > 0 && pdl));
         }
     }
     if (h->peer_on && (prc = vxrt_peer_after_denoise(h))) return prc;

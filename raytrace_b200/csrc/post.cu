@@ -43,7 +43,7 @@ __device__ __forceinline__ uint32_t lds_u16(const uint16_t* p) {
 // (r, g) sums, 2 also packs (b, weight sum) against a per-texel {b, 1.0} pair.  The kernel is issue-bound, so the
 // slots are what counts (the FMA pipe is busy the same number of cycles either way, misc/ubench/f32x2.cu).
 #ifndef VXRT_DN_PACK
-#define VXRT_DN_PACK 3
+#define VXRT_DN_PACK 1
 #endif
 typedef unsigned long long dn_f2;
 __device__ __forceinline__ dn_f2 dn_pk(float lo, float hi) { dn_f2 r; asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
@@ -107,6 +107,11 @@ __global__ void __launch_bounds__(DN_TX * DN_TY, VXRT_DN_MINB) k_denoise(const u
                     const int y = ybase + (o + k) * S;
                     if (y < row1) { const size_t pi = (size_t)y * width + x; work |= (SWAP ? (uint32_t)__ldg(depth + pi) : (uint32_t)__ldg(normal + pi)) < 16u; }
                 }
+        // Programmatic dependent launch (passes 2..6): this grid may become resident while the previous pass drains;
+        // everything above reads only the trace pass's images.  From here on the previous pass is complete and visible,
+        // and the next pass may start taking the slots this one frees.  Both are no-ops in a plain launch.
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        asm volatile("griddepcontrol.launch_dependents;");
         if (!__syncthreads_or(work)) {
             if (x < width)
                 for (int o = threadIdx.y * DN_G; o < L; o += DN_TY * DN_G)
@@ -238,7 +243,7 @@ __global__ void __launch_bounds__(DN_TX * DN_TY, VXRT_DN_MINB) k_denoise(const u
 
 template <int S, int L>
 cudaError_t launch_denoise_s(const ushort4* src, ushort4* dst, const uint16_t* depth, const uint8_t* normal, int width,
-                             int height, int swap, int row0, int row1, cudaStream_t s) {
+                             int height, int swap, int row0, int row1, cudaStream_t s, bool pdl) {
     using T = DnTile<S, L>;
     const int rows = row1 - row0;
     const int per_res = (rows + S - 1) / S;                 // decimated rows of the fullest residue class
@@ -252,9 +257,15 @@ cudaError_t launch_denoise_s(const ushort4* src, ushort4* dst, const uint16_t* d
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    if (swap) k_denoise<S, L, true><<<grid, block, T::BYTES, s>>>(src, dst, depth, normal, width, height, row0, row1, groups);
-    else k_denoise<S, L, false><<<grid, block, T::BYTES, s>>>(src, dst, depth, normal, width, height, row0, row1, groups);
-    return cudaGetLastError();
+    cudaLaunchConfig_t lc;
+    memset(&lc, 0, sizeof lc);
+    lc.gridDim = grid; lc.blockDim = block; lc.dynamicSmemBytes = T::BYTES; lc.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = at; lc.numAttrs = pdl ? 1 : 0;
+    if (swap) return cudaLaunchKernelEx(&lc, k_denoise<S, L, true>, src, dst, depth, normal, width, height, row0, row1, groups);
+    return cudaLaunchKernelEx(&lc, k_denoise<S, L, false>, src, dst, depth, normal, width, height, row0, row1, groups);
 }
 
 // finalize.comp:21-31
@@ -361,14 +372,14 @@ cudaError_t vxrt_launch_row_cost(const uint32_t* steps, const uint8_t* rays, con
 }
 
 cudaError_t vxrt_launch_denoise(const ushort4* src, ushort4* dst, const uint16_t* depth, const uint8_t* normal,
-                                int width, int height, int size, int swap, int row0, int row1, cudaStream_t s) {
+                                int width, int height, int size, int swap, int row0, int row1, cudaStream_t s, bool pdl) {
     if (row1 <= row0) return cudaSuccess;
     switch (size) {                                        // pipeline.rs:103: sizes 1, 2, 4, 8, 8, 16
-        case 1: return launch_denoise_s<1, VXRT_DN_L0>(src, dst, depth, normal, width, height, swap, row0, row1, s);
-        case 2: return launch_denoise_s<2, VXRT_DN_L0>(src, dst, depth, normal, width, height, swap, row0, row1, s);
-        case 4: return launch_denoise_s<4, VXRT_DN_L0>(src, dst, depth, normal, width, height, swap, row0, row1, s);
-        case 8: return launch_denoise_s<8, VXRT_DN_L1>(src, dst, depth, normal, width, height, swap, row0, row1, s);
-        case 16: return launch_denoise_s<16, VXRT_DN_L1>(src, dst, depth, normal, width, height, swap, row0, row1, s);
+        case 1: return launch_denoise_s<1, VXRT_DN_L0>(src, dst, depth, normal, width, height, swap, row0, row1, s, pdl);
+        case 2: return launch_denoise_s<2, VXRT_DN_L0>(src, dst, depth, normal, width, height, swap, row0, row1, s, pdl);
+        case 4: return launch_denoise_s<4, VXRT_DN_L0>(src, dst, depth, normal, width, height, swap, row0, row1, s, pdl);
+        case 8: return launch_denoise_s<8, VXRT_DN_L1>(src, dst, depth, normal, width, height, swap, row0, row1, s, pdl);
+        case 16: return launch_denoise_s<16, VXRT_DN_L1>(src, dst, depth, normal, width, height, swap, row0, row1, s, pdl);
         default: return cudaErrorInvalidValue;
     }
 }
