@@ -667,6 +667,7 @@ int vxrt_render_frame(VxrtHandle* h) {
     if (h->d_hist[0]) h->hist_idx ^= 1;                                  // this frame's records; [hist_idx ^ 1] = the frame before
     P.hit_pos = h->d_hit_pos[h->hist_idx];
     P.counters = h->d_counters;
+    P.one2 = 0x3F8000003F800000ull;
 
     // the image goes to the buffer an asynchronous read-back is not using (vxrt_read_output_async)
     h->out_idx ^= 1;

@@ -46,6 +46,7 @@ struct TraceParams {
     float4* accum;
     float4* hit_pos;                     // VXRT_FLAG_REPROJECT: primary.position (offset, :166-180) + face bits; {0,0,0,16} on air
     unsigned long long* counters;        // [0]=rays [1]=steps [2]=hits [3]=noise fetches [4]=limit exhausted
+    unsigned long long one2;             // {1.0f, 1.0f}: a multiplicand ptxas cannot see through (trace_fast.cu (E14))
 };
 
 // temporal.cu: old_origin / old_transform_c0..2 of the frame block (pipeline.rs:213-227) and the images of the pass
