@@ -47,7 +47,8 @@ WORKLOADS = {
            "then 1080p full-lighting re-render, 512^3 biome world (BASELINE config 5)"),
 }
 EDITS_PER_FRAME = {"c5": 10000}
-IN_FLIGHT = {"c1": 2, "c2": 2, "c4": 1}          # frames in flight per GPU (--in-flight 0)
+IN_FLIGHT = {"c1": 2, "c2": 2, "c3": 1, "c4": 1}   # frames in flight per GPU (--in-flight 0); c3 can chain two handles through the
+                                                    # shared running sum (--in-flight 2) but measures no gain: 0.672 against 0.660 ms
 MODE_NAMES = {0: "primary", 1: "primary+shadow", 2: "full"}
 
 
@@ -243,7 +244,7 @@ def run_vxrt(args, rank, world_size, local_rank, shard="bands", dist=None):
     r.upload_blue_noise(noise)
     r.generate_world(kind, seed)                 # world replicated: every rank generates the same seeded world
     lib, h = N.lib, r.handle
-    chained = accumulate or args.workload in EDITS_PER_FRAME
+    chained = args.workload in EDITS_PER_FRAME    # (accumulation chains through the shared running sum: vxrt_create_shared)
     S = (args.in_flight or IN_FLIGHT.get(args.workload, 1)) if (world_size == 1 or by_frames) and not chained else 1
     # S handles on this GPU share r's world (one copy in HBM); frames go to them round-robin, so S frames are in flight
     rs = [r] + [R.Renderer(W, H, dims, mode, flags, device=local_rank, share_world=r) for _ in range(S - 1)]

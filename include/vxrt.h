@@ -129,7 +129,11 @@ int  vxrt_create(const VxrtConfig* cfg, VxrtHandle** out);
  * dims must equal the owner's.  World writes (uploads, generate, edits, blue noise) go through the owner only — on a
  * borrower they fail with VXRT_ERR_STATE; the owner waits for the borrowers' frames in flight before it writes, and a
  * borrower's next frame waits for the write.  Destroy borrowers before their owner (a borrower that outlives it has
- * no world and fails with VXRT_ERR_STATE). */
+ * no world and fails with VXRT_ERR_STATE).
+ * VXRT_FLAG_ACCUMULATE on a borrower (the owner must have it, same image and rows): the running sum is the owner's, so
+ * frames submitted alternately to owner and borrowers form ONE accumulation chain, exactly the frames of a single
+ * handle - each trace pass is ordered after the previous frame's, the denoise/finalize passes of frame k overlap the
+ * trace pass of frame k+1; vxrt_reset_accumulation on any handle of the group resets that sum. */
 int  vxrt_create_shared(const VxrtConfig* cfg, VxrtHandle* owner, VxrtHandle** out);
 /* replaces Drop for Pipeline/Core (pipeline.rs:258-277, core.rs:88-112) */
 void vxrt_destroy(VxrtHandle* h);

@@ -171,6 +171,19 @@ int world_write_end(VxrtHandle* h) {
     return VXRT_OK;
 }
 const VxrtHandle* world_of(const VxrtHandle* h) { return h->world_owner ? h->world_owner : h; }
+// the handle that keeps the accumulation chain's event: the owner of a shared running sum, else the handle itself
+VxrtHandle* accum_keeper(VxrtHandle* h) { return h->accum_borrowed ? h->world_owner : h; }
+// order this handle's stream after the last write of the running sum when another handle made it
+int accum_wait(VxrtHandle* h) {
+    VxrtHandle* k = accum_keeper(h);
+    if (k && k->ev_accum && k->accum_last && k->accum_last != h) CU(cudaStreamWaitEvent(h->stream, k->ev_accum, 0));
+    return VXRT_OK;
+}
+int accum_written(VxrtHandle* h) {
+    VxrtHandle* k = accum_keeper(h);
+    if (k && k->ev_accum && (!k->sharers.empty() || k != h)) { CU(cudaEventRecord(k->ev_accum, h->stream)); k->accum_last = h; }
+    return VXRT_OK;
+}
 
 int rebuild_dirty(VxrtHandle* h) {
     CU(vxrt_launch_build_minefield(h->d_materials, h->d_minefield, h->cfg.nx, h->cfg.ny, h->cfg.nz, h->d_dirty, h->stream));
@@ -375,7 +388,18 @@ static int create_impl(const VxrtConfig* cfg, VxrtHandle* owner, VxrtHandle** ou
             if ((rc = alloc_zero(h, (void**)&h->d_rays, P))) return rc;
             if ((rc = alloc_zero(h, (void**)&h->d_lighting_raw, P * 8))) return rc;
         }
-        if (cfg->flags & VXRT_FLAG_ACCUMULATE) if ((rc = alloc_zero(h, (void**)&h->d_accum, P * 16))) return rc;
+        if (cfg->flags & VXRT_FLAG_ACCUMULATE) {
+            if (owner) {                                                 // one running sum for the whole group of handles
+                if (!owner->d_accum || owner->cfg.width != cfg->width || owner->cfg.height != cfg->height || owner->row0 != h->row0 || owner->row1 != h->row1) {
+                    h->err = "vxrt_create_shared: VXRT_FLAG_ACCUMULATE needs an owner created with it and the same image and rows";
+                    return VXRT_ERR_INVALID;
+                }
+                h->d_accum = owner->d_accum; h->accum_borrowed = true;
+            } else {
+                if ((rc = alloc_zero(h, (void**)&h->d_accum, P * 16))) return rc;
+                CU(cudaEventCreateWithFlags(&h->ev_accum, cudaEventDisableTiming));
+            }
+        }
         if (cfg->flags & VXRT_FLAG_REPROJECT) {
             for (int i = 0; i < 2; i++) {
                 if ((rc = alloc_zero(h, (void**)&h->d_hit_pos[i], P * 16))) return rc;
@@ -389,6 +413,7 @@ static int create_impl(const VxrtConfig* cfg, VxrtHandle* owner, VxrtHandle** ou
     const int rc = init();
     if (rc != VXRT_OK) {
         if (owner) h->d_materials = nullptr, h->d_minefield = nullptr, h->d_noise = nullptr;
+        if (h->accum_borrowed) h->d_accum = nullptr;
         g_create_error = h->err; vxrt_destroy(h); return rc;
     }
     if (owner) { h->world_owner = owner; owner->sharers.push_back(h); h->world_seen = owner->world_version; }
@@ -416,12 +441,15 @@ void vxrt_destroy(VxrtHandle* h) {
         auto& v = h->world_owner->sharers;
         for (size_t i = 0; i < v.size(); i++) if (v[i] == h) { v.erase(v.begin() + i); break; }
         h->d_materials = nullptr; h->d_minefield = nullptr; h->d_noise = nullptr;
+        if (h->accum_borrowed) { h->d_accum = nullptr; if (h->world_owner->accum_last == h) h->world_owner->accum_last = nullptr; }
     }
     for (VxrtHandle* s : h->sharers) {           // an owner destroyed first leaves its borrowers without a world
         cudaStreamSynchronize(s->stream);
         s->world_owner = nullptr; s->d_materials = nullptr; s->d_minefield = nullptr; s->d_noise = nullptr;
         s->have_world = s->have_noise = false;
+        if (s->accum_borrowed) s->d_accum = nullptr;     // and without a running sum: their frames fail with VXRT_ERR_STATE
     }
+    if (h->ev_accum) cudaEventDestroy(h->ev_accum);
     if (h->ev_world) cudaEventDestroy(h->ev_world);
     void* ptrs[] = {h->d_materials, h->d_minefield, h->d_noise, h->d_lut, h->d_dirty, h->d_edits, h->d_lighting, h->d_pong,
                     h->d_lighting_raw, h->d_depth, h->d_normal, h->d_albedo, h->d_emission, h->d_fog, h->d_out_buf[0], h->d_out_buf[1],
@@ -593,8 +621,11 @@ int vxrt_reset_accumulation(VxrtHandle* h) {
     if (!h) return VXRT_ERR_INVALID;
     if (!h->d_accum) return fail(h, VXRT_ERR_STATE, "vxrt_reset_accumulation: handle created without VXRT_FLAG_ACCUMULATE");
     CU(cudaSetDevice(h->cfg.device));
+    int rc;
+    if ((rc = accum_wait(h))) return rc;
     CU(cudaMemsetAsync(h->d_accum, 0, pixels(h) * 16, h->stream));
-    h->frames_accumulated = 0;
+    if ((rc = accum_written(h))) return rc;
+    accum_keeper(h)->frames_accumulated = 0;
     return VXRT_OK;
 }
 
@@ -678,6 +709,7 @@ int vxrt_render_frame(VxrtHandle* h) {
         CU(cudaStreamWaitEvent(h->stream, h->world_owner->ev_world, 0));
         h->world_seen = h->world_owner->world_version;
     }
+    if (h->d_accum && (prc = accum_wait(h))) return prc;                // shared running sum: after the previous frame's trace pass
     CU(cudaMemsetAsync(h->d_counters, 0, 8 * sizeof(unsigned long long), h->stream));
     CU(cudaEventRecord(h->ev[0], h->stream));
     if (!h->peer_on) {
@@ -701,10 +733,11 @@ int vxrt_render_frame(VxrtHandle* h) {
         if (!n && (prc = vxrt_peer_push_halo(h))) return prc;
     }
     CU(cudaEventRecord(h->ev[1], h->stream));
+    if (h->d_accum && (prc = accum_written(h))) return prc;
     if (h->peer_on && (prc = vxrt_peer_wait_halo(h))) return prc;
     if (h->d_lighting_raw)
         CU(cudaMemcpyAsync(h->d_lighting_raw, h->d_lighting, pixels(h) * 8, cudaMemcpyDeviceToDevice, h->stream));
-    if (h->d_accum) h->frames_accumulated++;
+    if (h->d_accum) accum_keeper(h)->frames_accumulated++;
     if (h->d_hist[0]) {                                                  // temporal.cu; timed with the denoise passes
         ReprojectParams R;
         memset(&R, 0, sizeof R);
@@ -773,6 +806,8 @@ int vxrt_read_buffer(VxrtHandle* h, int buffer_id, void* dst, size_t nbytes) {
     if (!b.ptr) return fail(h, VXRT_ERR_STATE, "vxrt_read_buffer: buffer not allocated for this handle (check the create flags)");
     if (nbytes < b.bytes) return fail(h, VXRT_ERR_SIZE, "vxrt_read_buffer: host buffer too small");
     CU(cudaSetDevice(h->cfg.device));
+    int rc;
+    if (buffer_id == VXRT_BUF_ACCUM && (rc = accum_wait(h))) return rc;
     CU(cudaMemcpyAsync(dst, b.ptr, b.bytes, cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     return VXRT_OK;

@@ -241,6 +241,18 @@ __global__ void __launch_bounds__(DN_TX * DN_TY, VXRT_DN_MINB) k_denoise(const u
     }
 }
 
+// Launch priority of the passes after the trace pass (cudaLaunchAttributePriority), for several frames in flight on one
+// GPU.  Measured (misc/run_r.sh): at the highest priority C2 goes 0.278 -> 0.287 ms per frame and C3 0.672 -> 0.745, so
+// the default is the stream's priority; VXRT_POST_PRIORITY=1 turns it on.
+int post_priority() {
+    static const int p = [] {
+        const char* e = getenv("VXRT_POST_PRIORITY");
+        if (!e || atoi(e) == 0) return 0;
+        int lo = 0, hi = 0;
+        return cudaDeviceGetStreamPriorityRange(&lo, &hi) == cudaSuccess ? hi : 0;   // "greatest" priority is the lowest number
+    }();
+    return p;
+}
 template <int S, int L>
 cudaError_t launch_denoise_s(const ushort4* src, ushort4* dst, const uint16_t* depth, const uint8_t* normal, int width,
                              int height, int swap, int row0, int row1, cudaStream_t s, bool pdl) {
@@ -260,10 +272,11 @@ cudaError_t launch_denoise_s(const ushort4* src, ushort4* dst, const uint16_t* d
     cudaLaunchConfig_t lc;
     memset(&lc, 0, sizeof lc);
     lc.gridDim = grid; lc.blockDim = block; lc.dynamicSmemBytes = T::BYTES; lc.stream = s;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[0].val.programmaticStreamSerializationAllowed = 1;
-    lc.attrs = at; lc.numAttrs = pdl ? 1 : 0;
+    cudaLaunchAttribute at[2];
+    int na = 0;
+    if (post_priority() != 0) { at[na].id = cudaLaunchAttributePriority; at[na].val.priority = post_priority(); na++; }
+    if (pdl) { at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[na].val.programmaticStreamSerializationAllowed = 1; na++; }
+    lc.attrs = at; lc.numAttrs = na;
     if (swap) return cudaLaunchKernelEx(&lc, k_denoise<S, L, true>, src, dst, depth, normal, width, height, row0, row1, groups);
     return cudaLaunchKernelEx(&lc, k_denoise<S, L, false>, src, dst, depth, normal, width, height, row0, row1, groups);
 }
@@ -392,7 +405,14 @@ cudaError_t vxrt_launch_finalize(const uchar4* albedo, const uchar4* emission, c
     VxrtPeerTail none; memset(&none, 0, sizeof none);
     if (tail)       // peer tail: one fence + ticket per CTA, so keep the CTA count low
         k_finalize<true><<<ntiles > 148 * 8 ? 148 * 8 : ntiles, 256, 0, s>>>(albedo, emission, fog, lighting, depth, noise, out, width, height, row0, row1, *tail);
-    else
-        k_finalize<false><<<dim3((width + 31) / 32, (row1 - row0 + 7) / 8), 256, 0, s>>>(albedo, emission, fog, lighting, depth, noise, out, width, height, row0, row1, none);
+    else {
+        cudaLaunchConfig_t lc;
+        memset(&lc, 0, sizeof lc);
+        lc.gridDim = dim3((width + 31) / 32, (row1 - row0 + 7) / 8); lc.blockDim = dim3(256); lc.stream = s;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributePriority; at[0].val.priority = post_priority();
+        lc.attrs = at; lc.numAttrs = post_priority() != 0 ? 1 : 0;
+        return cudaLaunchKernelEx(&lc, k_finalize<false>, albedo, emission, fog, lighting, depth, noise, out, width, height, row0, row1, none);
+    }
     return cudaGetLastError();
 }

@@ -79,6 +79,10 @@ struct VxrtHandle {
     // device) and never writes them; the owner orders its world writes against the borrowers' frames (api.cu world_write_*)
     VxrtHandle* world_owner = nullptr; std::vector<VxrtHandle*> sharers;
     cudaEvent_t ev_world = nullptr; unsigned long long world_version = 0, world_seen = 0;
+    // VXRT_FLAG_ACCUMULATE on a borrower: the running sum is the owner's (accum_borrowed), so frames dealt alternately
+    // to owner and borrowers form ONE accumulation chain; a trace pass waits for the previous writer's (ev_accum, kept
+    // on the owner) and the passes after it overlap the next frame's trace pass
+    bool accum_borrowed = false; cudaEvent_t ev_accum = nullptr; VxrtHandle* accum_last = nullptr;
     uint32_t* d_materials; uint8_t* d_minefield; uint8_t* d_noise; float* d_lut;
     std::vector<uint8_t> h_noise;        // host copy: the seed texel is read on the host (raytrace.comp:298-303)
     uint32_t* d_dirty;                   // one flag per 64^3 chunk

@@ -536,3 +536,41 @@ def test_shared_world_handles_and_frames_in_flight(orc, world, noise):
     with R.Renderer(64, 64, (64, 64, 64)) as a:
         with pytest.raises(R.VxrtError):
             R.Renderer(64, 64, (128, 64, 64), share_world=a)
+
+
+def test_shared_accumulation_chain(orc, world, noise):
+    """VXRT_FLAG_ACCUMULATE on handles that share a world: ONE running sum (the owner's).  Frames dealt alternately
+    to owner and borrower accumulate exactly as on a single handle - each trace pass waits for the previous one, the
+    passes after it overlap the next frame's trace pass - and every frame's image equals the single-handle frame."""
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    dims = scenes.WORLDS["c1"][0]
+    m, f = world("c1")
+    W, H = 160, 96
+    flags = N.FLAG_DENOISE | N.FLAG_FINALIZE | N.FLAG_ACCUMULATE
+    blocks = [_frame_block(orc, dims, seed=s) for s in range(1, 8)]
+    with R.Renderer(W, H, dims, N.MODE_FULL, flags) as solo:
+        solo.upload_blue_noise(noise); solo.upload_world(m, f)
+        want = []
+        for b in blocks:
+            solo.set_frame(b); solo.render_frame()
+            want.append(solo.read_output().copy())
+        want_acc = solo.read_buffer(N.BUF_ACCUM).copy()
+        solo.reset_accumulation(); solo.set_frame(blocks[2]); solo.render_frame()
+        want_reset = solo.read_output().copy()
+    with R.FramePipeline(W, H, dims, N.MODE_FULL, flags, depth=2) as fp:
+        fp.owner.upload_blue_noise(noise); fp.owner.upload_world(m, f)
+        used = [fp.submit(b) for b in blocks]                      # nothing synchronised in between
+        got = {}
+        for k in (5, 6):                                               # the last frame of each handle is still in its image
+            got[k] = used[k].read_output()
+        assert np.array_equal(got[5], want[5]) and np.array_equal(got[6], want[6])
+        for r in fp.renderers:                                         # either handle reads the one running sum
+            assert np.array_equal(r.read_buffer(N.BUF_ACCUM), want_acc)
+        fp.renderers[1].reset_accumulation()                           # through the borrower: the chain's sum
+        r = fp.submit(blocks[2])
+        assert np.array_equal(r.read_output(), want_reset)
+        assert np.all(fp.owner.read_buffer(N.BUF_ACCUM)[..., 3] == 1.0)
+    with R.Renderer(W, H, dims, N.MODE_FULL, N.FLAG_DENOISE | N.FLAG_FINALIZE) as plain:   # owner without a running sum
+        with pytest.raises(R.VxrtError):
+            R.Renderer(W, H, dims, N.MODE_FULL, flags, share_world=plain)
