@@ -108,6 +108,9 @@ void orc_diffuse_luts(float sin1[256], float cos1[256], float sin2[256], float c
 int orc_trace(const OrcScene* scene, const uint8_t frame[192], int mode,
               OrcBuffers* out, int row0, int row1, OrcStats* stats, int n_threads);
 
+/* analysis hook (tests/analysis_divergence.py): while `log` is non-NULL, orc_trace stores the march length of each of a
+ * pixel's five rays (primary, sun1, dif1, sun2, dif2; 0 = not traced) at log[pixel * 5 + ray].  NULL turns it off. */
+void orc_set_ray_log(uint16_t* log);
 /* single ray, for known-answer tests.  out: [air, face, steps, word, voxel xyz] ; fout: [t, pos xyz] */
 void orc_trace_ray(const OrcScene* scene, const int32_t lr[3], const float origin[3],
                    const float dir[3], int32_t iout[7], float fout[4]);

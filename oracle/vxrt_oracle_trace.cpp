@@ -61,6 +61,7 @@ static inline uint32_t fetch_world(const Ctx& c, V3 p) {
 }
 
 /* raytrace.comp:82-183 */
+static uint16_t* g_ray_log = nullptr;   /* orc_set_ray_log: [w*h][5] march steps of primary, sun1, dif1, sun2, dif2 (0 = not traced) */
 static Hit trace_ray(const Ctx& c, V3 origin, V3 direction) {
     direction = normalize3(direction);                                  /* :83 */
     Hit r; memset(&r, 0, sizeof r);
@@ -168,6 +169,8 @@ static inline const uint8_t* noise_texel(const uint8_t* bn, float cx, float cy) 
 
 extern "C" {
 
+void orc_set_ray_log(uint16_t* log) { g_ray_log = log; }
+
 void orc_trace_ray(const OrcScene* scene, const int32_t lr[3], const float origin[3],
                    const float dir[3], int32_t iout[7], float fout[4]) {
     Ctx c; c.s = scene; c.st = 0;
@@ -225,6 +228,8 @@ int orc_trace(const OrcScene* scene, const uint8_t frame[192], int mode, OrcBuff
                 }
                 V3 light = v3(0, 0, 0);
                 Hit primary = trace_ray(c, ray_start, ray_dir);                                            /* :320 */
+                uint16_t* rl = g_ray_log ? g_ray_log + pi * 5 : nullptr;   /* analysis hook: march length of each of the five rays */
+                if (rl) { rl[0] = (uint16_t)primary.steps; rl[1] = rl[2] = rl[3] = rl[4] = 0; }
                 if (primary.air) {
                     light = sample_sky(ray_dir, sunangle, sunlight, true);                                 /* :322 */
                 } else if (mode != ORC_MODE_PRIMARY) {
@@ -232,10 +237,12 @@ int orc_trace(const OrcScene* scene, const uint8_t frame[192], int mode, OrcBuff
                     st.noise_fetches++;
                     V3 sun_dir = normalize3(add(sunangle, v3(((float)nv[0] / 255.0f) * 0.05f, ((float)nv[1] / 255.0f) * 0.05f, 0.0f * 0.05f))); /* :186 */
                     Hit sun1 = trace_ray(c, primary.position, sun_dir);                                    /* :325 */
+                    if (rl) rl[1] = (uint16_t)sun1.steps;
                     if (sun1.air) light = add(light, sunlight);
                     if (mode == ORC_MODE_FULL) {
                         V3 d1 = diffuse_direction(L, nv, primary.normal);                                  /* :329 */
                         Hit dif1 = trace_ray(c, primary.position, d1);                                     /* :330 */
+                        if (rl) rl[2] = (uint16_t)dif1.steps;
                         if (dif1.air) {
                             light = add(light, sample_sky(d1, sunangle, sunlight, true));
                         } else {
@@ -245,9 +252,11 @@ int orc_trace(const OrcScene* scene, const uint8_t frame[192], int mode, OrcBuff
                             st.noise_fetches++;
                             V3 sun_dir2 = normalize3(add(sunangle, v3(((float)nv2[0] / 255.0f) * 0.05f, ((float)nv2[1] / 255.0f) * 0.05f, 0.0f * 0.05f)));
                             Hit sun2 = trace_ray(c, dif1.position, sun_dir2);                              /* :337 */
+                            if (rl) rl[3] = (uint16_t)sun2.steps;
                             if (sun2.air) light2 = add(light2, sunlight);
                             V3 d2 = diffuse_direction(L, nv2, dif1.normal);                                /* :341 */
                             Hit dif2 = trace_ray(c, dif1.position, d2);                                    /* :342 */
+                            if (rl) rl[4] = (uint16_t)dif2.steps;
                             if (dif2.air) light2 = add(light2, sample_sky(d2, sunangle, sunlight, true));
                             light2 = mul(light2, dif1.albedo);                                             /* :346 */
                             /* + dif1.emission == 0 (:155, :347) */
