@@ -46,6 +46,11 @@ typedef enum VxrtMode { VXRT_MODE_PRIMARY = 0, VXRT_MODE_SHADOW = 1, VXRT_MODE_F
                                          frame block's old_origin / old_transform_c0..2, which the reference fills every
                                          frame (pipeline.rs:213-227) and its shaders never read; see vxrt_reset_history */
 #define VXRT_FLAG_REF_ROWS      0x20u /* leave the rows the reference grid (W/8,H/8+1) never writes untouched*/
+#define VXRT_FLAG_RAY_HANDOFF   0x100u /* FULL lighting: a pixel entering the second bounce level gives its diffuse ray to a
+                                          finished lane of its warp, so both rays of the level march in one round
+                                          (trace_fast.cu (E16)).  Same rays, same arithmetic, same images and frame
+                                          counters; ignored with VXRT_FLAG_HIT_BUFFERS (per-pixel counters) and on row
+                                          bands.  Off by default: measured 0.94x .. 1.06x depending on the scene */
 
 /* Replaces the compile-time constants of src/render/constants.rs:9-10,22-31 and the
  * shader constants raytrace.comp:37-60, which become run-time parameters. */

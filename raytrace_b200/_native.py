@@ -19,6 +19,7 @@ OK, ERR_INVALID, ERR_CUDA, ERR_STATE, ERR_SIZE, ERR_COMM = 0, -1, -2, -3, -4, -5
 MODE_PRIMARY, MODE_SHADOW, MODE_FULL = 0, 1, 2
 # vxrt_create flags
 FLAG_HIT_BUFFERS, FLAG_DENOISE, FLAG_FINALIZE, FLAG_ACCUMULATE, FLAG_PONG_SWAP, FLAG_REF_ROWS, FLAG_GENERAL_MARCH, FLAG_REPROJECT = 1, 2, 4, 8, 16, 32, 64, 128
+FLAG_RAY_HANDOFF = 256
 # VxrtBufferId
 (BUF_OUTPUT, BUF_LIGHTING, BUF_DEPTH, BUF_NORMAL, BUF_ALBEDO, BUF_EMISSION, BUF_FOG, BUF_HIT_VOXEL, BUF_HIT_FACE,
  BUF_HIT_WORD, BUF_HIT_T, BUF_STEPS, BUF_RAYS, BUF_ACCUM, BUF_LIGHTING_RAW, BUF_HIT_POS, BUF_HISTORY, BUF_COMPLETED) = range(18)

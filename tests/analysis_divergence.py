@@ -75,9 +75,20 @@ def main():
     for k, n in enumerate(NAMES):
         lanes = w[..., k].sum() / max(per_round[:, k].sum(), 1)
         print(f"      round {n:8s} {per_round[:, k].sum() / 1e6:8.2f} M warp-steps ({100 * per_round[:, k].sum() / base:4.1f} %), {lanes:5.1f} lanes")
-    # (a) level-2 rays of a warp packed into its idle lanes: sun2 and dif2 of the survivors share one round when they fit
+    # (a) level-2 rays of a warp packed into its idle lanes, longest first (needs the lengths): sun2 and dif2 of the
+    #     survivors share one round when they fit
     lvl2 = np.concatenate([w[..., 3], w[..., 4]], axis=1)
-    report("(a) sun2 + dif2 of a warp packed into one round (shuffle hand-off to idle lanes)", per_round[:, :3].sum() + packed_rounds(lvl2).sum())
+    report("(a) sun2 + dif2 of a warp packed into full rounds, longest rays first (needs the lengths)", per_round[:, :3].sum() + packed_rounds(lvl2).sum())
+    # (a') what trace_fast.cu (E16, VXRT_FLAG_RAY_HANDOFF) does: owners in lane order pair with the finished lanes; the
+    #      owners left without a partner still march dif2 in a fifth round
+    own = w[..., 3] > 0
+    n_own = own.sum(axis=1)
+    pairs = np.minimum(n_own, 32 - n_own)
+    rank = np.cumsum(own, axis=1) - 1
+    helped = own & (rank < pairs[:, None])
+    r4 = np.maximum(w[..., 3].max(axis=1), np.where(helped, w[..., 4], 0).max(axis=1))
+    r5 = np.where(own & ~helped, w[..., 4], 0).max(axis=1)
+    report("(a') as implemented (E16): lane-order pairing, unpaired owners march dif2 in a fifth round", per_round[:, :3].sum() + r4.sum() + r5.sum())
     # (b) both levels packed: sun1 + dif1 too (only helps warps with <= 16 ground pixels)
     lvl1 = np.concatenate([w[..., 1], w[..., 2]], axis=1)
     report("(b) (a) and sun1 + dif1 packed the same way", per_round[:, 0].sum() + packed_rounds(lvl1).sum() + packed_rounds(lvl2).sum())

@@ -574,3 +574,32 @@ def test_shared_accumulation_chain(orc, world, noise):
     with R.Renderer(W, H, dims, N.MODE_FULL, N.FLAG_DENOISE | N.FLAG_FINALIZE) as plain:   # owner without a running sum
         with pytest.raises(R.VxrtError):
             R.Renderer(W, H, dims, N.MODE_FULL, flags, share_world=plain)
+
+
+@pytest.mark.parametrize("scene,width,height", [("c1", 256, 256), ("mid", 320, 200), ("small", 72, 40)])
+def test_second_bounce_handoff_is_invisible(orc, world, noise, scene, width, height):
+    """trace_fast.cu (E16), VXRT_FLAG_RAY_HANDOFF: a FULL-lighting frame gives each second-bounce diffuse ray to a finished
+    lane of its warp.  Every ray and every operation of a pixel stays the same, so the images are those of the
+    sequential form (a handle with hit buffers) bit for bit, the frame counters too, and both match the oracle."""
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    dims = scenes.WORLDS[scene][0]
+    m, f = world(scene)
+    frames = [_frame_block(orc, dims, k, 3, seed=40 + k) for k in range(3)]
+    with R.Renderer(width, height, dims, N.MODE_FULL, N.FLAG_HIT_BUFFERS | N.FLAG_ACCUMULATE) as seq, \
+         R.Renderer(width, height, dims, N.MODE_FULL, N.FLAG_ACCUMULATE | N.FLAG_RAY_HANDOFF) as hand:
+        for r in (seq, hand):
+            r.upload_blue_noise(noise); r.upload_world(m, f)
+        fr = orc.Frame(width, height, accumulate=True)
+        for blk in frames:
+            ref = orc.render(m, f, noise, blk, N.MODE_FULL, width, height, frame=fr)
+            for r in (seq, hand):
+                r.set_frame(blk); r.render_frame()
+            for b in (N.BUF_LIGHTING, N.BUF_DEPTH, N.BUF_NORMAL, N.BUF_ALBEDO, N.BUF_FOG, N.BUF_ACCUM):
+                assert np.array_equal(seq.read_buffer(b), hand.read_buffer(b)), b
+            a, b = seq.frame_stats(), hand.frame_stats()
+            assert (a.rays, a.steps, a.hits, a.noise_fetches, a.limit_exhausted) == (b.rays, b.steps, b.hits, b.noise_fetches, b.limit_exhausted)
+            assert (b.rays, b.steps, b.hits) == (ref.stats.rays, ref.stats.steps, ref.stats.hits)
+            assert np.array_equal(hand.read_buffer(N.BUF_DEPTH), ref.depth) and np.array_equal(hand.read_buffer(N.BUF_NORMAL), ref.normal)
+            d = np.abs(hand.read_buffer(N.BUF_LIGHTING).astype(np.int64) - ref.lighting.astype(np.int64)).max()
+            assert d <= C16_TOL, d
