@@ -40,8 +40,10 @@ __device__ __forceinline__ uint32_t lds_u16(const uint16_t* p) {
     return r;
 }
 // Packed fp32 accumulation (sm_100a FFMA2 = fma.rn.f32x2, one issue slot for two lanes): VXRT_DN_PACK 1 packs the
-// (r, g) sums, 2 also packs (b, weight sum) against a per-texel {b, 1.0} pair.  The kernel is issue-bound, so the
-// slots are what counts (the FMA pipe is busy the same number of cycles either way, misc/ubench/f32x2.cu).
+// (r, g) sums (1976 -> 1840 SASS instructions per four outputs); 3 also packs (b, weight sum) against texels staged as
+// {r, g, b, 1.0} + {dist, normal} (1664 instructions, 24 B of shared memory per texel instead of 18); 2 builds the
+// {b, 1.0} pair in registers (the extra MOVs cancel the gain).  Measured: the passes are bound by their
+// tails, not by issue slots, so all of them are within 1 % of each other in time.
 #ifndef VXRT_DN_PACK
 #define VXRT_DN_PACK 1
 #endif
