@@ -366,6 +366,11 @@ def run_vxrt(args, rank, world_size, local_rank, shard="bands", dist=None):
     # page-locked host images -> vxrt_wait_output of the PREVIOUS frame (the double-buffered read-back of
     # include/vxrt.h: frame k's D2H copy overlaps frame k+1's kernels).  Every frame's 8.3 MB lands in host memory
     # inside the timed region.
+    if edits is not None:                        # the edit stream changes the world: replay it from the state the
+        r.generate_world(kind, seed)             # device-timed loop started from (untimed), so that both loops
+        for i in range(args.warmup):             # render the same sequence of worlds
+            step(i)
+        r.sync()
     reads = rank == 0 or by_frames               # frames mode: every rank delivers the frames it rendered to host memory
     out_host = [np.empty((H, W, 4), np.uint8) for _ in range(2 * S)]
     if reads:

@@ -166,7 +166,8 @@ int  vxrt_read_world(VxrtHandle* h, uint32_t* materials, uint8_t* minefield);   
 int  vxrt_upload_blue_noise(VxrtHandle* h, const uint8_t* rgba, size_t nbytes);
 
 /* ---- edits (no reference equivalent beyond set_block + pack_into, chunk.rs:115-184) -- */
-/* Writes the words, then rebuilds the minefield of every touched 64^3 chunk. */
+/* Writes the words, then rebuilds the minefield of every touched 64^3 chunk.  Asynchronous on the handle's stream; the
+ * list is copied (into page-locked staging) before the call returns, so the caller may reuse it at once. */
 int  vxrt_apply_edits(VxrtHandle* h, const VxrtEdit* edits, size_t n);
 /* Same with the edit list already on the device (e.g. after an NCCL broadcast). */
 int  vxrt_apply_edits_device(VxrtHandle* h, const void* d_edits, size_t n);

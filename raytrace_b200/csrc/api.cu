@@ -456,6 +456,7 @@ void vxrt_destroy(VxrtHandle* h) {
                     h->d_hit_voxel, h->d_hit_face, h->d_hit_word, h->d_hit_t, h->d_steps, h->d_rays, h->d_accum, h->d_counters,
                     h->d_hit_pos[0], h->d_hit_pos[1], h->d_hist[0], h->d_hist[1], h->d_completed};
     for (void* p : ptrs) if (p) cudaFree(p);
+    for (int i = 0; i < 2; i++) { if (h->h_edits[i]) cudaFreeHost(h->h_edits[i]); if (h->ev_edits[i]) cudaEventDestroy(h->ev_edits[i]); }
     for (int i = 0; i < 5; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     for (int i = 0; i < 2; i++) {
         if (h->ev_frame_done[i]) cudaEventDestroy(h->ev_frame_done[i]);
@@ -600,11 +601,25 @@ int vxrt_apply_edits(VxrtHandle* h, const VxrtEdit* edits, size_t n) {
         CU(cudaMalloc(&h->d_edits, cap * sizeof(VxrtEdit)));
         h->edits_cap = cap;
     }
-    CU(cudaMemcpyAsync(h->d_edits, edits, n * sizeof(VxrtEdit), cudaMemcpyHostToDevice, h->stream));
-    const int rc = vxrt_apply_edits_device(h, h->d_edits, n);
-    if (rc) return rc;
-    CU(cudaStreamSynchronize(h->stream));    // the host list may be reused on return
-    return VXRT_OK;
+    // the host list may be reused on return: it is copied into one of two page-locked staging buffers here, and the
+    // device copy runs from there in stream order - no wait for the frames already queued on the stream
+    if (n > h->h_edits_cap) {
+        CU(cudaStreamSynchronize(h->stream));
+        size_t cap = 1024; while (cap < n) cap *= 2;
+        for (int i = 0; i < 2; i++) {
+            if (h->h_edits[i]) CU(cudaFreeHost(h->h_edits[i]));
+            h->h_edits[i] = nullptr;
+            CU(cudaMallocHost(&h->h_edits[i], cap * sizeof(VxrtEdit)));
+            if (!h->ev_edits[i]) CU(cudaEventCreateWithFlags(&h->ev_edits[i], cudaEventDisableTiming));
+        }
+        h->h_edits_cap = cap;
+    }
+    const int slot = h->edit_slot ^= 1;
+    CU(cudaEventSynchronize(h->ev_edits[slot]));          // the copy out of this buffer two calls ago (done long since)
+    memcpy(h->h_edits[slot], edits, n * sizeof(VxrtEdit));
+    CU(cudaMemcpyAsync(h->d_edits, h->h_edits[slot], n * sizeof(VxrtEdit), cudaMemcpyHostToDevice, h->stream));
+    CU(cudaEventRecord(h->ev_edits[slot], h->stream));
+    return vxrt_apply_edits_device(h, h->d_edits, n);
 }
 
 // ---- per frame --------------------------------------------------------------------------------

@@ -87,6 +87,9 @@ struct VxrtHandle {
     std::vector<uint8_t> h_noise;        // host copy: the seed texel is read on the host (raytrace.comp:298-303)
     uint32_t* d_dirty;                   // one flag per 64^3 chunk
     void* d_edits; size_t edits_cap;
+    // vxrt_apply_edits stages the caller's list through two page-locked buffers, so it returns without waiting for the
+    // frames still queued on the stream (ev_edits[i]: the copy out of buffer i has been issued and completed)
+    void* h_edits[2] = {nullptr, nullptr}; size_t h_edits_cap = 0; cudaEvent_t ev_edits[2] = {nullptr, nullptr}; int edit_slot = 0;
     // frame images
     ushort4 *d_lighting, *d_pong, *d_lighting_raw;
     uint16_t* d_depth; uint8_t* d_normal; uchar4 *d_albedo, *d_emission, *d_fog, *d_output;
