@@ -199,7 +199,8 @@ def run_reference(args, rank, world_size):
     v = rays / total / 1e6
     line = {"metric": "Mrays/s", "value": v, "unit": "Mrays/s", "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3, "frames_per_s": args.steps / total,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "higher_is_better": True, "scaling": "strong" if (accumulate or ne) else "weak",   # the label of the vxrt arm's line
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": desc, "mode": MODE_NAMES[mode], "width": W, "height": H, "world": list(dims)},
             "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": cores, "kind": "port",
                              "sample": f"{args.steps} full frames (trace + 6 denoise + finalize) of the workload"},
@@ -435,7 +436,7 @@ def run_vxrt(args, rank, world_size, local_rank, shard="bands", dist=None):
         line = {
             "metric": "Mrays/s", "value": rays / (dev_ms / 1e3) / 1e6, "unit": "Mrays/s", "n_gpus": world_size,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps,
-            "frames_per_s": args.steps * nf / (dev_ms / 1e3), "higher_is_better": True, "scaling": "weak" if by_frames else "strong",
+            "frames_per_s": args.steps * nf / (dev_ms / 1e3), "higher_is_better": True, "scaling": "weak" if shard == "frames" else "strong",   # frames dealt to the GPUs: per-GPU work fixed as N grows
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": desc, "mode": MODE_NAMES[mode], "width": W, "height": H, "world": list(dims),
                        "passes": "trace + 6 denoise + finalize" + ("" if world_size == 1 or by_frames else " + NCCL band gather (bands re-trace their halo)"
