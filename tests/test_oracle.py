@@ -158,3 +158,27 @@ def test_generator_is_deterministic_and_edits_unique(orc):
     assert len(np.unique(e[:, :3], axis=0)) == 10000
     assert (np.abs(e[:, :3]) <= 256).all()
     assert set(np.unique(e[:, 3])) == {0, 0xCD9B3}
+
+
+def test_ray_log_agrees_with_the_pixel_counters(orc):
+    """orc_set_ray_log (the hook tests/analysis_divergence.py costs the march loop with): per pixel, the five logged
+    march lengths add up to the steps counter and the non-zero ones count the rays."""
+    from raytrace_b200 import scenes
+    dims, kind, seed = scenes.WORLDS["small"]
+    m, f = orc.build_minefield(orc.generate_world(*dims, kind, seed))
+    cam = scenes.camera(dims)
+    blk = orc.fill_frame(cam["origin"], cam["heading"], cam["pitch"], cam["sun_angle"], 3)
+    W, H = 96, 64
+    log = np.zeros((H, W, 5), np.uint16)
+    L = orc.lib()
+    L.orc_set_ray_log.argtypes = [orc.C.c_void_p]
+    L.orc_set_ray_log(orc._p(log))
+    try:
+        fr = orc.render(m, f, orc.blue_noise(), blk, orc.MODE_FULL, W, H)
+    finally:
+        L.orc_set_ray_log(None)
+    assert np.array_equal(log.sum(axis=2, dtype=np.uint32), fr.steps)
+    assert np.array_equal((log > 0).sum(axis=2).astype(np.uint8), fr.rays)
+    assert np.all(log[..., 0] > 0)                                   # every pixel has a primary ray
+    assert np.all((log[..., 3] > 0) == (log[..., 4] > 0))            # sun2 and dif2 come together
+    assert np.all((log[..., 3] == 0) | (log[..., 2] > 0))            # and only after dif1
