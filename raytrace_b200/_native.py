@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-# VXRT_LIB: another build of the same library (A/B runs of kernel variants, misc/run_k.sh); never a fallback
+# VXRT_LIB: another build of the same library (A/B runs of kernel variants, misc/r1_runs/run_k.sh); never a fallback
 LIB_PATH = os.environ.get("VXRT_LIB") or os.path.join(_HERE, "libvxrt.so")
 
 ABI_VERSION = 1

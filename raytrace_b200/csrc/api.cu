@@ -701,6 +701,10 @@ int vxrt_render_frame(VxrtHandle* h) {
                   P.max_steps <= 200000;                  // k_trace_fast packs 5 * max_steps into 20 bits
         const float o[3] = {P.ox, P.oy, P.oz}, l[3] = {P.lrx, P.lry, P.lrz}, d[3] = {(float)P.nx, (float)P.ny, (float)P.nz};
         for (int a = 0; a < 3; a++) ok = ok && fabsf(o[a]) + d[a] + 128.0f < lim && fabsf(l[a]) + d[a] + 128.0f < lim;
+        // raytrace.comp:312-315 moves the start by (space / dir.y + 1e-4) * dir when -origin.y > H: unbounded for pixels
+        // whose |dir.y| is tiny, so the bound on |origin| says nothing about the relocated start.  The camera is outside
+        // the window there anyway: the general kernel renders those frames.
+        if (-P.oy > P.hy) ok = false;
         P.fast = ok ? 1 : 0;
         for (int a = 0; a < 3; a++) sky_thresholds(l[a], d[a] * 0.5f, &P.sky_lo[a], &P.sky_hi[a]);
     }

@@ -244,7 +244,7 @@ __global__ void __launch_bounds__(DN_TX * DN_TY, VXRT_DN_MINB) k_denoise(const u
 }
 
 // Launch priority of the passes after the trace pass (cudaLaunchAttributePriority), for several frames in flight on one
-// GPU.  Measured (misc/run_r.sh): at the highest priority C2 goes 0.278 -> 0.287 ms per frame and C3 0.672 -> 0.745, so
+// GPU.  Measured (misc/r1_runs/run_r.sh): at the highest priority C2 goes 0.278 -> 0.287 ms per frame and C3 0.672 -> 0.745, so
 // the default is the stream's priority; VXRT_POST_PRIORITY=1 turns it on.
 int post_priority() {
     static const int p = [] {
