@@ -182,3 +182,23 @@ def test_ray_log_agrees_with_the_pixel_counters(orc):
     assert np.all(log[..., 0] > 0)                                   # every pixel has a primary ray
     assert np.all((log[..., 3] > 0) == (log[..., 4] > 0))            # sun2 and dif2 come together
     assert np.all((log[..., 3] == 0) | (log[..., 2] > 0))            # and only after dif1
+
+
+def test_scene_edit_stream_and_frame_blocks_match_oracle(orc):
+    """raytrace_b200/scenes.py defines the benchmark's inputs without the oracle: its integer edit stream must equal
+    orc_generate_edits bit for bit, and its frame blocks orc_fill_frame's up to the last bit of host trigonometry
+    (blocks are inputs of the boundary; both bench arms use scenes.py's)."""
+    from raytrace_b200 import scenes
+    for dims in [(512, 512, 512), (256, 256, 256), (128, 128, 128), (2048, 2048, 256)]:
+        for n, fr in [(10000, 0), (2000, 3), (7, 1), (1, 0)]:
+            a, b = orc.generate_edits(n, *dims, 7, fr), scenes.edit_stream(n, dims, 7, fr)
+            assert np.array_equal(a, b), (dims, n, fr)
+            assert len(np.unique(b[:, :3], axis=0)) == n
+    with pytest.raises(ValueError):
+        scenes.edit_stream(4, (64, 64, 64), 7, 0)
+    for i in (0, 17, 63):
+        cam = scenes.camera((512, 512, 512), i, 64)
+        a = orc.fill_frame(cam["origin"], cam["heading"], cam["pitch"], cam["sun_angle"], i + 1, (16, 0, -32))
+        b = np.frombuffer(scenes.frame_block(cam, i + 1, (16, 0, -32)), np.uint8)
+        assert b.size == 192 and np.array_equal(a[:32], b[:32]) and np.array_equal(a[80:], b[80:])
+        assert np.abs(a[32:80].view(np.float32) - b[32:80].view(np.float32)).max() <= 2 ** -23
