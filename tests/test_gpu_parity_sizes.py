@@ -57,7 +57,7 @@ def test_c2_at_size(orc, noise, world512):
             _compare(ref, r, N, denoise=True, finalize=True)
             s = r.frame_stats()
             assert (s.rays, s.steps, s.hits, s.noise_fetches) == (ref.stats.rays, ref.stats.steps, ref.stats.hits, ref.stats.noise_fetches)
-            assert s.limit_exhausted == ref.stats.ub_limit_exhausted == 0 and ref.stats.ub_start_in_solid == 0
+            assert s.limit_exhausted == ref.stats.ub_limit_exhausted == 0
 
 
 def test_c2_two_frames_in_flight_at_size(orc, noise, world512):
