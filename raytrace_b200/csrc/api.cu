@@ -81,6 +81,16 @@ void value_tables(float* lut, int width, int height) {
     }
 }
 
+// trace_fast.cu writes the albedo image as 2n + (n >> 6) per 7-bit field: the same byte as UNORM8(n / 127) with this host's
+// fp32 operations (the sequence of raytrace.comp:156-158 + the RGBA8 store), for every n
+bool albedo_bytes_ok() {
+    for (int n = 0; n < 128; n++) {
+        volatile float q = (float)n / 127.0f; volatile float c = q < 0.0f ? 0.0f : (q > 1.0f ? 1.0f : q); volatile float v = c * 255.0f;
+        if ((int)nearbyintf(v) != 2 * n + (n >> 6)) return false;
+    }
+    return true;
+}
+
 // (E8) trace_fast.cu: g(p) = fl(p - lr) is monotone in p, so {p : |g(p)| >= H} = {p <= lo} U {p >= hi}.
 // lo/hi are found by bisection over the floats in their numeric order.
 uint32_t float_key(float f) { uint32_t u; memcpy(&u, &f, 4); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
@@ -301,6 +311,7 @@ static int create_impl(const VxrtConfig* cfg, VxrtHandle* owner, VxrtHandle** ou
         if (cfg->flags & VXRT_FLAG_ACCUMULATE) { g_create_error = "vxrt_create: VXRT_FLAG_REPROJECT excludes VXRT_FLAG_ACCUMULATE"; return VXRT_ERR_INVALID; }
         if (row0 != 0 || row1 != cfg->height) { g_create_error = "vxrt_create: VXRT_FLAG_REPROJECT needs the whole frame on one handle"; return VXRT_ERR_INVALID; }
     }
+    if (!albedo_bytes_ok()) { g_create_error = "vxrt_create: UNORM8(n / 127) != 2n + (n >> 6) on this host (trace_fast.cu albedo image)"; return VXRT_ERR_INVALID; }
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0) {
