@@ -175,6 +175,15 @@ int world_write_begin(VxrtHandle* h, const char* who) {
     return VXRT_OK;
 }
 int world_write_end(VxrtHandle* h) {
+    if (h->field_arr) {                          // layout A/B: the texture's copy of the occupancy field follows every world write
+        cudaMemcpy3DParms p;
+        memset(&p, 0, sizeof p);
+        p.srcPtr = make_cudaPitchedPtr(h->d_minefield, (size_t)h->cfg.nx, (size_t)h->cfg.nx, (size_t)h->cfg.ny);
+        p.dstArray = h->field_arr;
+        p.extent = make_cudaExtent((size_t)h->cfg.nx, (size_t)h->cfg.ny, (size_t)h->cfg.nz);
+        p.kind = cudaMemcpyDeviceToDevice;
+        CU(cudaMemcpy3DAsync(&p, h->stream));
+    }
     if (h->sharers.empty()) return VXRT_OK;
     CU(cudaEventRecord(h->ev_world, h->stream));
     h->world_version++;
@@ -372,6 +381,20 @@ static int create_impl(const VxrtConfig* cfg, VxrtHandle* owner, VxrtHandle** ou
             if ((rc = alloc_zero(h, (void**)&h->d_minefield, V))) return rc;
             if ((rc = alloc_zero(h, (void**)&h->d_noise, h->h_noise.size()))) return rc;
             if ((rc = alloc_zero(h, (void**)&h->d_dirty, (size_t)(cfg->nx >> 6) * (cfg->ny >> 6) * (cfg->nz >> 6) * 4))) return rc;
+            const char* fm = getenv("VXRT_FIELD");
+            h->field_mode = !fm ? 0 : !strcmp(fm, "tex") ? 1 : !strcmp(fm, "texn") ? 2 : 0;
+            if (h->field_mode) {
+                cudaChannelFormatDesc cd = cudaCreateChannelDesc<unsigned char>();
+                CU(cudaMalloc3DArray(&h->field_arr, &cd, make_cudaExtent((size_t)cfg->nx, (size_t)cfg->ny, (size_t)cfg->nz)));
+                cudaResourceDesc rd; memset(&rd, 0, sizeof rd);
+                rd.resType = cudaResourceTypeArray; rd.res.array.array = h->field_arr;
+                for (int i = 0; i < 2; i++) {
+                    cudaTextureDesc td; memset(&td, 0, sizeof td);
+                    td.filterMode = cudaFilterModePoint; td.readMode = cudaReadModeElementType; td.normalizedCoords = i;
+                    for (int a = 0; a < 3; a++) td.addressMode[a] = i ? cudaAddressModeWrap : cudaAddressModeClamp;
+                    CU(cudaCreateTextureObject(&h->field_tex[i], &rd, &td, nullptr));
+                }
+            }
         }
         if ((rc = alloc_zero(h, (void**)&h->d_counters, 8 * sizeof(unsigned long long)))) return rc;
         std::vector<float> lut((size_t)VXRT_LUT_SCREEN + cfg->width + cfg->height);
@@ -460,6 +483,8 @@ void vxrt_destroy(VxrtHandle* h) {
         s->have_world = s->have_noise = false;
         if (s->accum_borrowed) s->d_accum = nullptr;     // and without a running sum: their frames fail with VXRT_ERR_STATE
     }
+    for (int i = 0; i < 2; i++) if (h->field_tex[i] && !h->world_owner) cudaDestroyTextureObject(h->field_tex[i]);
+    if (h->field_arr && !h->world_owner) cudaFreeArray(h->field_arr);
     if (h->ev_accum) cudaEventDestroy(h->ev_accum);
     if (h->ev_world) cudaEventDestroy(h->ev_world);
     void* ptrs[] = {h->d_materials, h->d_minefield, h->d_noise, h->d_lut, h->d_dirty, h->d_edits, h->d_lighting, h->d_pong,
@@ -729,6 +754,8 @@ int vxrt_render_frame(VxrtHandle* h) {
     P.hit_pos = h->d_hit_pos[h->hist_idx];
     P.counters = h->d_counters;
     P.one2 = 0x3F8000003F800000ull;
+    P.field = wo->field_mode; P.field_tex = wo->field_mode ? (unsigned long long)wo->field_tex[wo->field_mode - 1] : 0ull;
+    P.inx = 1.0f / (float)P.nx; P.iny = 1.0f / (float)P.ny; P.inz = 1.0f / (float)P.nz;
 
     // the image goes to the buffer an asynchronous read-back is not using (vxrt_read_output_async)
     h->out_idx ^= 1;

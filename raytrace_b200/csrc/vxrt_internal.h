@@ -47,6 +47,9 @@ struct TraceParams {
     float4* hit_pos;                     // VXRT_FLAG_REPROJECT: primary.position (offset, :166-180) + face bits; {0,0,0,16} on air
     unsigned long long* counters;        // [0]=rays [1]=steps [2]=hits [3]=noise fetches [4]=limit exhausted
     unsigned long long one2;             // {1.0f, 1.0f}: a multiplicand ptxas cannot see through (trace_fast.cu (E14))
+    // occupancy field as a 3-D texture over a block-linear cudaArray (layout A/B): 0 = linear array + LDG,
+    // 1 = integer texel coordinates, 2 = normalised coordinates with wrap addressing (the unit does the floor and the mod)
+    int field; unsigned long long field_tex; float inx, iny, inz;
 };
 
 // temporal.cu: old_origin / old_transform_c0..2 of the frame block (pipeline.rs:213-227) and the images of the pass
@@ -84,6 +87,9 @@ struct VxrtHandle {
     // on the owner) and the passes after it overlap the next frame's trace pass
     bool accum_borrowed = false; cudaEvent_t ev_accum = nullptr; VxrtHandle* accum_last = nullptr;
     uint32_t* d_materials; uint8_t* d_minefield; uint8_t* d_noise; float* d_lut;
+    // layout A/B (VXRT_FIELD=tex|texn at create): a copy of the occupancy field in a block-linear cudaArray, refreshed after every
+    // world write, read through texture objects [0] = integer coordinates, [1] = normalised + wrap
+    int field_mode = 0; cudaArray_t field_arr = nullptr; cudaTextureObject_t field_tex[2] = {0, 0};
     std::vector<uint8_t> h_noise;        // host copy: the seed texel is read on the host (raytrace.comp:298-303)
     uint32_t* d_dirty;                   // one flag per 64^3 chunk
     void* d_edits; size_t edits_cap;
