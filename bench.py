@@ -583,9 +583,12 @@ def run_vxrt(args, rank, world_size, local_rank, shard="bands", dist=None):
                          "ncu": {k: prof.get(k) for k in ("issue_active_pct", "lanes_per_instruction", "warp_instructions", "l2_hit_pct", "source")} if prof else None,
                          "note": "k_trace_fast is bound by instruction issue, not by memory (the ncu figures beside this note; the touched part of the "
                                  "occupancy field is L2-resident on the 512^3 world); frac is reported against HBM as the contract asks"},
-            "roofline_kernels": [
-                kroof("k_denoise (6 passes)", 19 * 6 * own_px, tot["denoise_ms"], 6, "19 B/pixel/pass: read 8+2+1, write 8 (SURVEY 8d)"),
-                kroof("k_finalize", 30 * own_px, tot["finalize_ms"], 1, "30 B/pixel: read 4+4+4+8+2+4, write 4 (SURVEY 8d)")],
+            "roofline_kernels": (
+                [kroof("k_denoise (6 passes, finalize.comp folded into the last)", (19 * 6 + 22) * own_px, tot["denoise_ms"] + tot["finalize_ms"], 6,
+                       "19 B/pixel/pass: read 8+2+1, write 8; the last pass also reads 4+4+4+4 (albedo, emission, fog, noise) and writes the 4 B output (SURVEY 8d minus finalize's 8 B lighting + 2 B depth re-read)")]
+                if launches_per_frame == 7 else
+                [kroof("k_denoise (6 passes)", 19 * 6 * own_px, tot["denoise_ms"], 6, "19 B/pixel/pass: read 8+2+1, write 8 (SURVEY 8d)"),
+                 kroof("k_finalize", 30 * own_px, tot["finalize_ms"], 1, "30 B/pixel: read 4+4+4+8+2+4, write 4 (SURVEY 8d)")]),
             "clocks": clk, "wall_s_timed_loop": wall,
         }
         if sustained:

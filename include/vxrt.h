@@ -211,6 +211,9 @@ size_t vxrt_buffer_bytes(const VxrtHandle* h, int buffer_id);
 void* vxrt_device_buffer(VxrtHandle* h, int buffer_id);     /* zero-copy consumers (NCCL gather) */
 void* vxrt_cuda_stream(VxrtHandle* h);                      /* cudaStream_t of the handle         */
 int  vxrt_frame_stats(VxrtHandle* h, VxrtFrameStats* out);  /* syncs the stream                   */
+/* Kernels one vxrt_render_frame launches on this handle outside peer mode: the trace pass, the six denoise passes, k_finalize
+ * (VXRT_FOLD=1 in the environment folds it into the last denoise launch), k_reproject with VXRT_FLAG_REPROJECT. */
+int  vxrt_launches_per_frame(const VxrtHandle* h);
 
 /* ---- image-space sharding plan: pure host arithmetic, usable without a device ------------------------ */
 /* rows[2r], rows[2r+1] = band [begin,end) of rank r: contiguous, edges on multiples of 8 rows

@@ -93,6 +93,7 @@ SYMBOLS = {
     "vxrt_device_buffer": (C.c_void_p, [_H, C.c_int]),
     "vxrt_cuda_stream": (C.c_void_p, [_H]),
     "vxrt_frame_stats": (C.c_int, [_H, C.POINTER(VxrtFrameStats)]),
+    "vxrt_launches_per_frame": (C.c_int, [_H]),
     "vxrt_plan_bands": (C.c_int, [C.c_int, C.c_int, C.c_void_p]),
     "vxrt_plan_bands_weighted": (C.c_int, [C.c_int, C.c_int, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "vxrt_row_costs": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_size_t]),

@@ -808,18 +808,31 @@ int vxrt_render_frame(VxrtHandle* h) {
         R.hist_prev = h->d_hist[h->hist_idx ^ 1]; R.hist_cur = h->d_hist[h->hist_idx];
         CU(vxrt_launch_reproject(R, h->stream));
     }
+    bool fold = false;
     if (h->cfg.flags & VXRT_FLAG_DENOISE) {
         // pipeline.rs:98-115: even passes lighting -> pong, odd passes pong -> lighting.  A band shrinks
         // by 3*size rows per pass towards [row0,row1) so that only valid rows are ever read.
         // passes 2..6 follow a denoise launch directly: programmatic dependent launch (post.cu) lets a pass become
         // resident while its predecessor drains
         static const bool pdl = getenv("VXRT_NO_PDL") == nullptr;
+        static const bool want_fold = getenv("VXRT_FOLD") != nullptr;
+        // VXRT_FOLD=1: finalize.comp rides on the last pass (one launch, one grid tail and a read of the lighting image less).
+        // Measured on the B200 (r2_h, C2): six passes + finalize 0.1915 ms apart, 0.1938 ms folded - the last pass's tiles
+        // (128 x 128 pixels at dilation 16) finish later with the extra loads and the flipped-row stores than the 0.016 ms
+        // finalize grid costs on its own - so the separate launch stays the default.
+        fold = (h->cfg.flags & VXRT_FLAG_FINALIZE) && !h->peer_on && want_fold;
         for (int k = 0; k < 6; k++) {
             const int r0 = h->plan[2 + 2 * k], r1 = h->plan[3 + 2 * k];
             const bool odd = (k & 1) != 0;
             const int swap = (odd && (h->cfg.flags & VXRT_FLAG_PONG_SWAP)) ? 1 : 0;
+            VxrtFinalizeFold ff = {h->d_albedo, h->d_emission, h->d_fog, h->d_noise, h->d_output, h->row0, h->row1};
+            if (k == 5 && fold && h->copy_pending[h->out_idx]) {            // the output image may still be on its way to the host
+                CU(cudaStreamWaitEvent(h->stream, h->ev_copy_done[h->out_idx], 0));
+                h->copy_pending[h->out_idx] = false;
+            }
             CU(vxrt_launch_denoise(odd ? h->d_pong : h->d_lighting, odd ? h->d_lighting : h->d_pong, h->d_depth, h->d_normal,
-                                   h->cfg.width, h->cfg.height, kDenoiseSizes[k], swap, r0, r1, h->stream, k > 0 && pdl));
+                                   h->cfg.width, h->cfg.height, kDenoiseSizes[k], swap, r0, r1, h->stream, k > 0 && pdl,
+                                   k == 5 && fold ? &ff : nullptr));
         }
     }
     if (h->peer_on && (prc = vxrt_peer_after_denoise(h))) return prc;
@@ -828,7 +841,7 @@ int vxrt_render_frame(VxrtHandle* h) {
         CU(cudaStreamWaitEvent(h->stream, h->ev_copy_done[h->out_idx], 0));
         h->copy_pending[h->out_idx] = false;
     }
-    if (h->cfg.flags & VXRT_FLAG_FINALIZE) {
+    if ((h->cfg.flags & VXRT_FLAG_FINALIZE) && !fold) {
         VxrtPeerTail tail;
         if (h->peer_on) tail = vxrt_peer_finalize_tail(h);
         CU(vxrt_launch_finalize(h->d_albedo, h->d_emission, h->d_fog, h->d_lighting, h->d_depth, h->d_noise,
@@ -839,6 +852,13 @@ int vxrt_render_frame(VxrtHandle* h) {
     CU(cudaEventRecord(h->ev[3], h->stream));
     h->rendered = true;
     return VXRT_OK;
+}
+
+int vxrt_launches_per_frame(const VxrtHandle* h) {
+    if (!h) return VXRT_ERR_INVALID;
+    const bool dn = (h->cfg.flags & VXRT_FLAG_DENOISE) != 0, fin = (h->cfg.flags & VXRT_FLAG_FINALIZE) != 0;
+    const bool fold = dn && fin && !h->peer_on && getenv("VXRT_FOLD") != nullptr;
+    return 1 + (dn ? 6 : 0) + (fin && !fold ? 1 : 0) + (h->d_hist[0] ? 1 : 0);
 }
 
 int vxrt_sync(VxrtHandle* h) {

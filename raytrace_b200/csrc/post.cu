@@ -85,11 +85,49 @@ __host__ __device__ constexpr float dn_weight(int ax, int ay) {
          : (lo == 0 ? 0.002289f : lo == 1 ? 0.001445f : 0.0f);
 }
 
-template <int S, int L, bool SWAP>
+// finalize.comp:21-31
+__device__ __forceinline__ float filmic_curve(float x) {
+    if (x < 0.3f) return x * x;
+    else if (x < 1.13333f) return fmaf(x, 0.6f, -0.09f);
+    else if (x < 2.5f) return fmaf(-0.219512195116f * (x - 2.5f), x - 2.5f, 1.0f);
+    else return 1.0f;
+}
+
+// finalize.comp:33-64 for one pixel whose lighting texel is already in registers.  Colour work under the tolerance contract
+// (<= 1/255 per channel): UNORM decodes are reciprocal multiplies folded into the constants, FMA contraction allowed.
+struct FinalizeImages { const uchar4* albedo; const uchar4* emission; const uchar4* fog; const uint16_t* depth; const uint8_t* noise; uchar4* out; int row0, row1; };
+__device__ __forceinline__ void finalize_pixel(const FinalizeImages& F, int width, int height, int x, int y, ushort4 l) {
+    const size_t pi = (size_t)y * width + x;
+    const uchar4 a = __ldg(F.albedo + pi), e = __ldg(F.emission + pi), f = __ldg(F.fog + pi);
+    const uint32_t d = __ldg(F.depth + pi);
+    const uchar4 bn = __ldg(reinterpret_cast<const uchar4*>(F.noise) + (y & 511) * VXRT_NOISE_SIZE + (x & 511));   // :55-57
+    const float fog_amount = fminf((float)d * (1.0f / (32.0f * 128.0f * 8.0f)), 1.0f);   // :47-48
+    const float av[3] = {(float)a.x, (float)a.y, (float)a.z}, ev[3] = {(float)e.x, (float)e.y, (float)e.z},
+                fv[3] = {(float)f.x, (float)f.y, (float)f.z}, lv[3] = {(float)l.x, (float)l.y, (float)l.z},
+                nv[3] = {(float)bn.x, (float)bn.y, (float)bn.z};
+    uint32_t o[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        float v = fmaf(av[k] * lv[k], 16.0f / (255.0f * 65535.0f), ev[k] * (4.0f / 255.0f));   // :36-40
+        if (d < 0xFFFF) v = fmaf(fv[k] * (2.0f / 255.0f) - v, fog_amount, v);                    // :44-50 mix(v, fog*2, amount)
+        v = fmaf(nv[k], 1.0f / (255.0f * 128.0f), filmic_curve(v));                               // :52-58
+        o[k] = __float2uint_rn(__saturatef(v) * 255.0f);
+    }
+    F.out[(size_t)(height - y - 1) * width + x] = make_uchar4((unsigned char)o[0], (unsigned char)o[1], (unsigned char)o[2], 255);   // :60-63
+}
+
+// FIN: the last pass also runs finalize.comp on every pixel it stores (pipeline.rs:117-123 folded into pipeline.rs:98-115's last
+// dispatch): the lighting texel goes to the lighting image as before AND, from registers, through finalize_pixel - one launch,
+// one grid tail and 8 B/pixel of reads less per frame.
+template <int S, int L, bool SWAP, bool FIN>
 __global__ void __launch_bounds__(DN_TX * DN_TY, VXRT_DN_MINB) k_denoise(const ushort4* __restrict__ src, ushort4* __restrict__ dst,
                                                    const uint16_t* __restrict__ depth, const uint8_t* __restrict__ normal,
-                                                   int width, int height, int row0, int row1, int groups) {
+                                                   int width, int height, int row0, int row1, int groups, const __grid_constant__ FinalizeImages F) {
     using T = DnTile<S, L>;
+    auto put = [&](int y, size_t pi, ushort4 v) {
+        dst[pi] = v;
+        if (FIN && y >= F.row0 && y < F.row1) finalize_pixel(F, width, height, (int)(pi - (size_t)y * width), y, v);
+    };
     extern __shared__ float4 dn_tile[];
     uint16_t* dn_nrm = reinterpret_cast<uint16_t*>(dn_tile + T::N);
     float2* dn_aux = reinterpret_cast<float2*>(dn_tile + T::N);       // VXRT_DN_PACK == 3
@@ -120,7 +158,7 @@ __global__ void __launch_bounds__(DN_TX * DN_TY, VXRT_DN_MINB) k_denoise(const u
 #pragma unroll
                     for (int k = 0; k < DN_G; k++) {
                         const int y = ybase + (o + k) * S;
-                        if (y < row1) { const size_t pi = (size_t)y * width + x; dst[pi] = __ldg(src + pi); }
+                        if (y < row1) { const size_t pi = (size_t)y * width + x; put(y, pi, __ldg(src + pi)); }
                     }
             return;
         }
@@ -169,7 +207,7 @@ __global__ void __launch_bounds__(DN_TX * DN_TY, VXRT_DN_MINB) k_denoise(const u
 #pragma unroll
             for (int k = 0; k < DN_G; k++) {
                 const int y = ybase + (o0 + k) * S;
-                if (y < row1) { const size_t pi = (size_t)y * width + x; dst[pi] = __ldg(src + pi); }
+                if (y < row1) { const size_t pi = (size_t)y * width + x; put(y, pi, __ldg(src + pi)); }
             }
             continue;
         }
@@ -233,11 +271,11 @@ __global__ void __launch_bounds__(DN_TX * DN_TY, VXRT_DN_MINB) k_denoise(const u
             dn_unpk(sbw[k], sb[k], tw[k]);
 #endif
             if (cn[k] >= 16) {
-                dst[pi] = __ldg(src + pi);                                     // :88-89
+                put(y, pi, __ldg(src + pi));                                   // :88-89
             } else {
                 const float inv = rcp_fast(tw[k]);
-                dst[pi] = make_ushort4((unsigned short)unorm_store(sr[k] * inv, 65535.0f), (unsigned short)unorm_store(sg[k] * inv, 65535.0f),
-                                       (unsigned short)unorm_store(sb[k] * inv, 65535.0f), 65535);   // :87
+                put(y, pi, make_ushort4((unsigned short)unorm_store(sr[k] * inv, 65535.0f), (unsigned short)unorm_store(sg[k] * inv, 65535.0f),
+                                        (unsigned short)unorm_store(sb[k] * inv, 65535.0f), 65535));   // :87
             }
         }
     }
@@ -255,9 +293,9 @@ int post_priority() {
     }();
     return p;
 }
-template <int S, int L>
+template <int S, int L, bool FIN>
 cudaError_t launch_denoise_s(const ushort4* src, ushort4* dst, const uint16_t* depth, const uint8_t* normal, int width,
-                             int height, int swap, int row0, int row1, cudaStream_t s, bool pdl) {
+                             int height, int swap, int row0, int row1, cudaStream_t s, bool pdl, const FinalizeImages& F) {
     using T = DnTile<S, L>;
     const int rows = row1 - row0;
     const int per_res = (rows + S - 1) / S;                 // decimated rows of the fullest residue class
@@ -266,8 +304,8 @@ cudaError_t launch_denoise_s(const ushort4* src, ushort4* dst, const uint16_t* d
     static_assert(L % DN_G == 0, "tile height must be a multiple of the outputs per thread");
     static bool attr_set = false;                           // per template instantiation
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(k_denoise<S, L, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T::BYTES);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_denoise<S, L, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T::BYTES);
+        cudaError_t e = cudaFuncSetAttribute(k_denoise<S, L, false, FIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T::BYTES);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_denoise<S, L, true, FIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T::BYTES);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
@@ -279,16 +317,8 @@ cudaError_t launch_denoise_s(const ushort4* src, ushort4* dst, const uint16_t* d
     if (post_priority() != 0) { at[na].id = cudaLaunchAttributePriority; at[na].val.priority = post_priority(); na++; }
     if (pdl) { at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[na].val.programmaticStreamSerializationAllowed = 1; na++; }
     lc.attrs = at; lc.numAttrs = na;
-    if (swap) return cudaLaunchKernelEx(&lc, k_denoise<S, L, true>, src, dst, depth, normal, width, height, row0, row1, groups);
-    return cudaLaunchKernelEx(&lc, k_denoise<S, L, false>, src, dst, depth, normal, width, height, row0, row1, groups);
-}
-
-// finalize.comp:21-31
-__device__ __forceinline__ float filmic_curve(float x) {
-    if (x < 0.3f) return x * x;
-    else if (x < 1.13333f) return fmaf(x, 0.6f, -0.09f);
-    else if (x < 2.5f) return fmaf(-0.219512195116f * (x - 2.5f), x - 2.5f, 1.0f);
-    else return 1.0f;
+    if (swap) return cudaLaunchKernelEx(&lc, k_denoise<S, L, true, FIN>, src, dst, depth, normal, width, height, row0, row1, groups, F);
+    return cudaLaunchKernelEx(&lc, k_denoise<S, L, false, FIN>, src, dst, depth, normal, width, height, row0, row1, groups, F);
 }
 
 // finalize.comp:33-64.  Colour work under the tolerance contract (<= 1/255 per channel): UNORM decodes are
@@ -313,24 +343,8 @@ __global__ void __launch_bounds__(256) k_finalize(const uchar4* __restrict__ alb
     const int ty = PEER ? tile / tiles_x : blockIdx.y, tx = PEER ? tile - ty * tiles_x : blockIdx.x;
     const int x = tx * 32 + (threadIdx.x & 31), y = row0 + ty * 8 + (threadIdx.x >> 5);
     if (x >= width || y >= row1) continue;
-    const size_t pi = (size_t)y * width + x;
-    const uchar4 a = __ldg(albedo + pi), e = __ldg(emission + pi), f = __ldg(fog + pi);
-    const ushort4 l = __ldg(lighting + pi);
-    const uint32_t d = __ldg(depth + pi);
-    const uchar4 bn = __ldg(reinterpret_cast<const uchar4*>(noise) + (y & 511) * VXRT_NOISE_SIZE + (x & 511));   // :55-57
-    const float fog_amount = fminf((float)d * (1.0f / (32.0f * 128.0f * 8.0f)), 1.0f);   // :47-48
-    const float av[3] = {(float)a.x, (float)a.y, (float)a.z}, ev[3] = {(float)e.x, (float)e.y, (float)e.z},
-                fv[3] = {(float)f.x, (float)f.y, (float)f.z}, lv[3] = {(float)l.x, (float)l.y, (float)l.z},
-                nv[3] = {(float)bn.x, (float)bn.y, (float)bn.z};
-    uint32_t o[3];
-#pragma unroll
-    for (int k = 0; k < 3; k++) {
-        float v = fmaf(av[k] * lv[k], 16.0f / (255.0f * 65535.0f), ev[k] * (4.0f / 255.0f));   // :36-40
-        if (d < 0xFFFF) v = fmaf(fv[k] * (2.0f / 255.0f) - v, fog_amount, v);                    // :44-50 mix(v, fog*2, amount)
-        v = fmaf(nv[k], 1.0f / (255.0f * 128.0f), filmic_curve(v));                               // :52-58
-        o[k] = __float2uint_rn(__saturatef(v) * 255.0f);
-    }
-    out[(size_t)(height - y - 1) * width + x] = make_uchar4((unsigned char)o[0], (unsigned char)o[1], (unsigned char)o[2], 255);   // :60-63
+    const FinalizeImages F = {albedo, emission, fog, depth, noise, out, row0, row1};
+    finalize_pixel(F, width, height, x, y, __ldg(lighting + (size_t)y * width + x));
     }
     if (PEER && tail.n_post) {                             // the last CTA to finish publishes the frame number
         __shared__ bool last;
@@ -371,11 +385,11 @@ __global__ void __launch_bounds__(256) k_row_cost(const uint32_t* __restrict__ s
 // CUDA loads a kernel's code at its first launch, and that load cannot complete while another kernel is resident
 // and spinning on a flag (peer.cu).  Every kernel of this file is therefore loaded when a handle is created.
 #define VXRT_PRELOAD(k) do { cudaFuncAttributes a_; cudaError_t e_ = cudaFuncGetAttributes(&a_, k); if (e_ != cudaSuccess) return e_; } while (0)
-template <int S, int L> cudaError_t preload_denoise() { VXRT_PRELOAD((k_denoise<S, L, false>)); VXRT_PRELOAD((k_denoise<S, L, true>)); return cudaSuccess; }
+template <int S, int L, bool FIN> cudaError_t preload_denoise() { VXRT_PRELOAD((k_denoise<S, L, false, FIN>)); VXRT_PRELOAD((k_denoise<S, L, true, FIN>)); return cudaSuccess; }
 cudaError_t vxrt_preload_post() {
     cudaError_t e;
-    if ((e = preload_denoise<1, VXRT_DN_L0>()) || (e = preload_denoise<2, VXRT_DN_L0>()) || (e = preload_denoise<4, VXRT_DN_L0>()) ||
-        (e = preload_denoise<8, VXRT_DN_L1>()) || (e = preload_denoise<16, VXRT_DN_L1>())) return e;
+    if ((e = preload_denoise<1, VXRT_DN_L0, false>()) || (e = preload_denoise<2, VXRT_DN_L0, false>()) || (e = preload_denoise<4, VXRT_DN_L0, false>()) ||
+        (e = preload_denoise<8, VXRT_DN_L1, false>()) || (e = preload_denoise<16, VXRT_DN_L1, false>()) || (e = preload_denoise<16, VXRT_DN_L1, true>())) return e;
     VXRT_PRELOAD(k_finalize<false>); VXRT_PRELOAD(k_finalize<true>); VXRT_PRELOAD(k_row_cost);
     return cudaSuccess;
 }
@@ -387,14 +401,21 @@ cudaError_t vxrt_launch_row_cost(const uint32_t* steps, const uint8_t* rays, con
 }
 
 cudaError_t vxrt_launch_denoise(const ushort4* src, ushort4* dst, const uint16_t* depth, const uint8_t* normal,
-                                int width, int height, int size, int swap, int row0, int row1, cudaStream_t s, bool pdl) {
+                                int width, int height, int size, int swap, int row0, int row1, cudaStream_t s, bool pdl, const VxrtFinalizeFold* fold) {
     if (row1 <= row0) return cudaSuccess;
+    FinalizeImages F; memset(&F, 0, sizeof F);
+    if (fold) {                                            // the last pass (size 16) with finalize.comp folded in
+        if (size != 16) return cudaErrorInvalidValue;
+        F.albedo = fold->albedo; F.emission = fold->emission; F.fog = fold->fog; F.depth = depth; F.noise = fold->noise; F.out = fold->out;
+        F.row0 = fold->row0; F.row1 = fold->row1;
+        return launch_denoise_s<16, VXRT_DN_L1, true>(src, dst, depth, normal, width, height, swap, row0, row1, s, pdl, F);
+    }
     switch (size) {                                        // pipeline.rs:103: sizes 1, 2, 4, 8, 8, 16
-        case 1: return launch_denoise_s<1, VXRT_DN_L0>(src, dst, depth, normal, width, height, swap, row0, row1, s, pdl);
-        case 2: return launch_denoise_s<2, VXRT_DN_L0>(src, dst, depth, normal, width, height, swap, row0, row1, s, pdl);
-        case 4: return launch_denoise_s<4, VXRT_DN_L0>(src, dst, depth, normal, width, height, swap, row0, row1, s, pdl);
-        case 8: return launch_denoise_s<8, VXRT_DN_L1>(src, dst, depth, normal, width, height, swap, row0, row1, s, pdl);
-        case 16: return launch_denoise_s<16, VXRT_DN_L1>(src, dst, depth, normal, width, height, swap, row0, row1, s, pdl);
+        case 1: return launch_denoise_s<1, VXRT_DN_L0, false>(src, dst, depth, normal, width, height, swap, row0, row1, s, pdl, F);
+        case 2: return launch_denoise_s<2, VXRT_DN_L0, false>(src, dst, depth, normal, width, height, swap, row0, row1, s, pdl, F);
+        case 4: return launch_denoise_s<4, VXRT_DN_L0, false>(src, dst, depth, normal, width, height, swap, row0, row1, s, pdl, F);
+        case 8: return launch_denoise_s<8, VXRT_DN_L1, false>(src, dst, depth, normal, width, height, swap, row0, row1, s, pdl, F);
+        case 16: return launch_denoise_s<16, VXRT_DN_L1, false>(src, dst, depth, normal, width, height, swap, row0, row1, s, pdl, F);
         default: return cudaErrorInvalidValue;
     }
 }

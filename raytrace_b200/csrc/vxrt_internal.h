@@ -136,8 +136,11 @@ cudaError_t vxrt_preload_world(); cudaError_t vxrt_preload_peer(); cudaError_t v
 // launchers (each returns the cudaGetLastError() of its launch)
 cudaError_t vxrt_launch_trace(const TraceParams& p, cudaStream_t s);        // dispatches on p.fast
 cudaError_t vxrt_launch_trace_fast(const TraceParams& p, cudaStream_t s);
+// finalize.comp folded into the last denoise pass (post.cu k_denoise<.., FIN>): the images finalize reads besides lighting/depth
+struct VxrtFinalizeFold { const uchar4* albedo; const uchar4* emission; const uchar4* fog; const uint8_t* noise; uchar4* out; int row0, row1; };
 cudaError_t vxrt_launch_denoise(const ushort4* src, ushort4* dst, const uint16_t* depth, const uint8_t* normal,
-                                int width, int height, int size, int swap, int row0, int row1, cudaStream_t s, bool pdl);
+                                int width, int height, int size, int swap, int row0, int row1, cudaStream_t s, bool pdl,
+                                const VxrtFinalizeFold* fold = nullptr);
 cudaError_t vxrt_launch_finalize(const uchar4* albedo, const uchar4* emission, const uchar4* fog, const ushort4* lighting,
                                  const uint16_t* depth, const uint8_t* noise, uchar4* out, int width, int height,
                                  int row0, int row1, cudaStream_t s, const VxrtPeerTail* tail = nullptr);
