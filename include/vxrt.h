@@ -45,7 +45,7 @@ typedef enum VxrtMode { VXRT_MODE_PRIMARY = 0, VXRT_MODE_SHADOW = 1, VXRT_MODE_F
 #define VXRT_FLAG_REPROJECT     0x80u /* temporal reprojection under camera motion (extension): reads the
                                          frame block's old_origin / old_transform_c0..2, which the reference fills every
                                          frame (pipeline.rs:213-227) and its shaders never read; see vxrt_reset_history */
-#define VXRT_FLAG_REF_ROWS      0x20u /* leave the rows the reference grid (W/8,H/8+1) never writes untouched*/
+/* 0x20 is unassigned (a reference-rows mode was declared here and never built: every pixel row is rendered, deviation D1) */
 #define VXRT_FLAG_RAY_HANDOFF   0x100u /* FULL lighting: a pixel entering the second bounce level gives its diffuse ray to a
                                           finished lane of its warp, so both rays of the level march in one round
                                           (trace_fast.cu (E16)).  Same rays, same arithmetic, same images and frame
@@ -162,12 +162,18 @@ int  vxrt_generate_world(VxrtHandle* h, int kind, uint32_t seed);
 /* Rebuild every chunk's minefield from the material words (pack_into, chunk.rs:125-184). */
 int  vxrt_rebuild_minefield(VxrtHandle* h);
 int  vxrt_read_world(VxrtHandle* h, uint32_t* materials, uint8_t* minefield);   /* either may be NULL */
+/* Stored-chunk check (chunk_storage.rs:56-68: a chunk file carries materials || minefield): compares the 64^3 occupancy bytes
+ * of a file (vxrt_chunk_decode) with the ones the device holds for window chunk (cx,cy,cz) - after vxrt_upload_chunk(materials,
+ * NULL) those are the ones k_build_minefield derived from the file's words with the pack_into rule (chunk.rs:125-184).
+ * *mismatches = differing bytes; *first_offset (may be NULL) = offset of the first one in the chunk, -1 if none. */
+int  vxrt_validate_chunk(VxrtHandle* h, int cx, int cy, int cz, const uint8_t* stored_minefield, uint64_t* mismatches, int64_t* first_offset);
 /* replaces create_blue_noise (render_data.rs:110-133): 512*512 RGBA8 */
 int  vxrt_upload_blue_noise(VxrtHandle* h, const uint8_t* rgba, size_t nbytes);
 
 /* ---- edits (no reference equivalent beyond set_block + pack_into, chunk.rs:115-184) -- */
-/* Writes the words, then rebuilds the minefield of every touched 64^3 chunk.  Asynchronous on the handle's stream; the
- * list is copied (into page-locked staging) before the call returns, so the caller may reuse it at once. */
+/* Writes the words, then rebuilds the minefield of every touched 64^3 chunk.  A voxel named more than once takes the word of
+ * its LAST entry in the list (set_block applied in list order, chunk.rs:115-117) on every replica.  Asynchronous on the
+ * handle's stream; the list is copied (into page-locked staging) before the call returns, so the caller may reuse it at once. */
 int  vxrt_apply_edits(VxrtHandle* h, const VxrtEdit* edits, size_t n);
 /* Same with the edit list already on the device (e.g. after an NCCL broadcast). */
 int  vxrt_apply_edits_device(VxrtHandle* h, const void* d_edits, size_t n);

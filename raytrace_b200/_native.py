@@ -18,7 +18,7 @@ OK, ERR_INVALID, ERR_CUDA, ERR_STATE, ERR_SIZE, ERR_COMM = 0, -1, -2, -3, -4, -5
 # VxrtMode (truncations of raytrace.comp:main, :320-350)
 MODE_PRIMARY, MODE_SHADOW, MODE_FULL = 0, 1, 2
 # vxrt_create flags
-FLAG_HIT_BUFFERS, FLAG_DENOISE, FLAG_FINALIZE, FLAG_ACCUMULATE, FLAG_PONG_SWAP, FLAG_REF_ROWS, FLAG_GENERAL_MARCH, FLAG_REPROJECT = 1, 2, 4, 8, 16, 32, 64, 128
+FLAG_HIT_BUFFERS, FLAG_DENOISE, FLAG_FINALIZE, FLAG_ACCUMULATE, FLAG_PONG_SWAP, FLAG_GENERAL_MARCH, FLAG_REPROJECT = 1, 2, 4, 8, 16, 64, 128
 FLAG_RAY_HANDOFF = 256
 # VxrtBufferId
 (BUF_OUTPUT, BUF_LIGHTING, BUF_DEPTH, BUF_NORMAL, BUF_ALBEDO, BUF_EMISSION, BUF_FOG, BUF_HIT_VOXEL, BUF_HIT_FACE,
@@ -75,6 +75,7 @@ SYMBOLS = {
     "vxrt_generate_world": (C.c_int, [_H, C.c_int, C.c_uint32]),
     "vxrt_rebuild_minefield": (C.c_int, [_H]),
     "vxrt_read_world": (C.c_int, [_H, C.c_void_p, C.c_void_p]),
+    "vxrt_validate_chunk": (C.c_int, [_H, C.c_int, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_int64)]),
     "vxrt_upload_blue_noise": (C.c_int, [_H, C.c_void_p, C.c_size_t]),
     "vxrt_apply_edits": (C.c_int, [_H, C.c_void_p, C.c_size_t]),
     "vxrt_apply_edits_device": (C.c_int, [_H, C.c_void_p, C.c_size_t]),

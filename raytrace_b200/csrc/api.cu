@@ -487,7 +487,7 @@ void vxrt_destroy(VxrtHandle* h) {
     if (h->field_arr && !h->world_owner) cudaFreeArray(h->field_arr);
     if (h->ev_accum) cudaEventDestroy(h->ev_accum);
     if (h->ev_world) cudaEventDestroy(h->ev_world);
-    void* ptrs[] = {h->d_materials, h->d_minefield, h->d_noise, h->d_lut, h->d_dirty, h->d_edits, h->d_lighting, h->d_pong,
+    void* ptrs[] = {h->d_materials, h->d_minefield, h->d_noise, h->d_lut, h->d_dirty, h->d_edits, h->d_edit_table, h->d_lighting, h->d_pong,
                     h->d_lighting_raw, h->d_depth, h->d_normal, h->d_albedo, h->d_emission, h->d_fog, h->d_out_buf[0], h->d_out_buf[1],
                     h->d_hit_voxel, h->d_hit_face, h->d_hit_word, h->d_hit_t, h->d_steps, h->d_rays, h->d_accum, h->d_counters,
                     h->d_hit_pos[0], h->d_hit_pos[1], h->d_hist[0], h->d_hist[1], h->d_completed};
@@ -595,6 +595,30 @@ int vxrt_read_world(VxrtHandle* h, uint32_t* materials, uint8_t* minefield) {
     return VXRT_OK;
 }
 
+int vxrt_validate_chunk(VxrtHandle* h, int cx, int cy, int cz, const uint8_t* stored_minefield, uint64_t* mismatches, int64_t* first_offset) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (!stored_minefield || !mismatches) return fail(h, VXRT_ERR_INVALID, "vxrt_validate_chunk: NULL argument");
+    if (cx < 0 || cy < 0 || cz < 0 || cx >= (h->cfg.nx >> 6) || cy >= (h->cfg.ny >> 6) || cz >= (h->cfg.nz >> 6))
+        return fail(h, VXRT_ERR_INVALID, "vxrt_validate_chunk: chunk coordinate outside the window");
+    const VxrtHandle* wo = world_of(h);
+    if (!wo->have_world) return fail(h, VXRT_ERR_STATE, "vxrt_validate_chunk: no world uploaded");
+    CU(cudaSetDevice(h->cfg.device));
+    uint8_t* d_stored = nullptr; unsigned long long* d_out = nullptr;
+    CU(cudaMalloc((void**)&d_stored, VXRT_CHUNK * VXRT_CHUNK * VXRT_CHUNK));
+    cudaError_t e = cudaMalloc((void**)&d_out, 16);
+    unsigned long long init[2] = {0ull, ~0ull}, res[2] = {0, 0};
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_stored, stored_minefield, VXRT_CHUNK * VXRT_CHUNK * VXRT_CHUNK, cudaMemcpyHostToDevice, h->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_out, init, 16, cudaMemcpyHostToDevice, h->stream);
+    if (e == cudaSuccess) e = vxrt_launch_compare_chunk(h->d_minefield, d_stored, h->cfg.nx, h->cfg.ny, cx, cy, cz, d_out, h->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(res, d_out, 16, cudaMemcpyDeviceToHost, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    cudaFree(d_stored); if (d_out) cudaFree(d_out);
+    CU(e);
+    *mismatches = res[0];
+    if (first_offset) *first_offset = res[0] ? (int64_t)res[1] : -1;
+    return VXRT_OK;
+}
+
 int vxrt_upload_blue_noise(VxrtHandle* h, const uint8_t* rgba, size_t nbytes) {
     if (!h) return VXRT_ERR_INVALID;
     if (!rgba) return fail(h, VXRT_ERR_INVALID, "vxrt_upload_blue_noise: rgba is NULL");
@@ -618,7 +642,16 @@ int vxrt_apply_edits_device(VxrtHandle* h, const void* d_edits, size_t n) {
     if (n == 0) return VXRT_OK;
     CU(cudaSetDevice(h->cfg.device));
     { const int wrc = world_write_begin(h, "vxrt_apply_edits_device"); if (wrc) return wrc; }
-    CU(vxrt_launch_apply_edits(h->d_materials, h->d_dirty, (const VxrtEdit*)d_edits, n, h->cfg.nx, h->cfg.ny, h->cfg.nz, h->stream));
+    if (h->edit_table_slots < 4 * n) {
+        size_t slots = 4096; while (slots < 4 * n) slots *= 2;
+        CU(cudaStreamSynchronize(h->stream));
+        if (h->d_edit_table) CU(cudaFree(h->d_edit_table));
+        h->d_edit_table = nullptr; h->edit_table_slots = 0;
+        CU(cudaMalloc(&h->d_edit_table, slots * 12));
+        h->edit_table_slots = slots;
+    }
+    CU(vxrt_launch_apply_edits(h->d_materials, h->d_dirty, (const VxrtEdit*)d_edits, n, h->cfg.nx, h->cfg.ny, h->cfg.nz,
+                               h->d_edit_table, h->edit_table_slots, h->stream));
     { const int rc = rebuild_dirty(h); if (rc) return rc; }
     return world_write_end(h);
 }
@@ -854,6 +887,20 @@ int vxrt_render_frame(VxrtHandle* h) {
     return VXRT_OK;
 }
 
+// peer-memory frames (peer.cu): a wait on another rank's flag that ran into its bound leaves an error word; whoever synchronises
+// with the frame next learns of it (the image may hold rows that never arrived) and the word is cleared
+static int peer_check(VxrtHandle* h) {
+    if (!h->peer_on) return VXRT_OK;
+    uint32_t perr = 0;
+    const int rc = vxrt_peer_error_word(h, &perr);
+    if (rc) return rc;
+    if (perr) {
+        vxrt_peer_clear_error(h);
+        return fail(h, VXRT_ERR_COMM, "peer-memory frame: a wait on another rank's flag timed out (ranks out of step?); the frame is incomplete");
+    }
+    return VXRT_OK;
+}
+
 int vxrt_launches_per_frame(const VxrtHandle* h) {
     if (!h) return VXRT_ERR_INVALID;
     const bool dn = (h->cfg.flags & VXRT_FLAG_DENOISE) != 0, fin = (h->cfg.flags & VXRT_FLAG_FINALIZE) != 0;
@@ -865,7 +912,7 @@ int vxrt_sync(VxrtHandle* h) {
     if (!h) return VXRT_ERR_INVALID;
     CU(cudaSetDevice(h->cfg.device));
     CU(cudaStreamSynchronize(h->stream));
-    return VXRT_OK;
+    return peer_check(h);
 }
 
 // ---- output -----------------------------------------------------------------------------------
@@ -887,7 +934,7 @@ int vxrt_read_buffer(VxrtHandle* h, int buffer_id, void* dst, size_t nbytes) {
     if (buffer_id == VXRT_BUF_ACCUM && (rc = accum_wait(h))) return rc;
     CU(cudaMemcpyAsync(dst, b.ptr, b.bytes, cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
-    return VXRT_OK;
+    return peer_check(h);
 }
 
 int vxrt_read_output(VxrtHandle* h, uint8_t* rgba8, size_t nbytes) { return vxrt_read_buffer(h, VXRT_BUF_OUTPUT, rgba8, nbytes); }
@@ -919,7 +966,7 @@ int vxrt_wait_output(VxrtHandle* h, uint64_t ticket) {
     for (int i = 0; i < 2; i++)
         if (h->ticket_of_buf[i] >= ticket && (pick < 0 || h->ticket_of_buf[i] < h->ticket_of_buf[pick])) pick = i;
     if (pick >= 0) CU(cudaEventSynchronize(h->ev_copy_done[pick]));
-    return VXRT_OK;
+    return peer_check(h);
 }
 
 int vxrt_host_register(VxrtHandle* h, void* ptr, size_t nbytes) {
@@ -969,9 +1016,7 @@ int vxrt_frame_stats(VxrtHandle* h, VxrtFrameStats* out) {
     unsigned long long c[8];
     CU(cudaMemcpyAsync(c, h->d_counters, sizeof c, cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
-    uint32_t perr = 0;
-    { const int rc = vxrt_peer_error_word(h, &perr); if (rc) return rc; }
-    if (perr) return fail(h, VXRT_ERR_COMM, "peer-memory frame: a wait on another rank's flag timed out (ranks out of step?)");
+    { const int rc = peer_check(h); if (rc) return rc; }
     out->rays = c[0]; out->steps = c[1]; out->hits = c[2]; out->noise_fetches = c[3]; out->limit_exhausted = c[4];
     CU(cudaEventElapsedTime(&out->trace_ms, h->ev[0], h->ev[1]));
     CU(cudaEventElapsedTime(&out->denoise_ms, h->ev[1], h->ev[2]));

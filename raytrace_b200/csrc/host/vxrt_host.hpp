@@ -109,12 +109,112 @@ class Game {
     float sun_angle_ = 0.f;
 };
 
+
+// src/render/pipeline/terrain_upload.rs: the sliding window.  Same positions, request queue and policy as the reference
+// (Position :22-47, request_increase :292-322, request_decrease :324-349, request_move_towards :351-367, one 16-voxel slab per
+// frame :277-286, render offset :29-36) with the window size taken from the handle.  A slab is gathered as ONE world box and
+// rotated into texel order, texel_i = (world_i - origin_i * 64) mod N_i (the identity the reference's chunk-piece copies
+// :84-211 implement); the toroidal scatter on the device is vxrt_upload_slice.
+class TerrainUploadManager {
+  public:
+    struct Position {
+        long origin[3]; int num_loaded_slices[3];
+        void render_offset(const int root_chunks[3], int out[3]) const {                                  // :29-36
+            for (int i = 0; i < 3; i++) out[i] = (int)((origin[i] + root_chunks[i] / 2) * constants::CHUNK_SIZE + num_loaded_slices[i] * constants::SLICE_SIZE);
+        }
+    };
+    struct Request { long origin[3]; int num_slices[3]; int axis; Position new_position; };
+
+    TerrainUploadManager(int nx, int ny, int nz) : window_{nx, ny, nz} {
+        for (int i = 0; i < 3; i++) {
+            root_chunks_[i] = window_[i] / constants::CHUNK_SIZE; slices_per_axis_[i] = window_[i] / constants::SLICE_SIZE;
+            cpu_.origin[i] = gpu_.origin[i] = -(root_chunks_[i] / 2);                                       // Position::default, :39-46
+            cpu_.num_loaded_slices[i] = gpu_.num_loaded_slices[i] = 0;
+        }
+    }
+    void request_increase(int axis) {                                                                       // :292-322
+        const Position old = cpu_;
+        cpu_.num_loaded_slices[axis] += 1;
+        if (cpu_.num_loaded_slices[axis] == slices_per_axis_[axis]) { cpu_.num_loaded_slices[axis] = 0; cpu_.origin[axis] += root_chunks_[axis]; }
+        Request r;
+        for (int i = 0; i < 3; i++) { r.origin[i] = old.origin[i]; r.num_slices[i] = old.num_loaded_slices[i]; }
+        r.origin[axis] += root_chunks_[axis];
+        r.axis = axis; r.new_position = cpu_;
+        queue_.push_back(r);
+    }
+    void request_decrease(int axis) {                                                                       // :324-349
+        if (cpu_.num_loaded_slices[axis] == 0) { cpu_.num_loaded_slices[axis] = slices_per_axis_[axis]; cpu_.origin[axis] -= root_chunks_[axis]; }
+        cpu_.num_loaded_slices[axis] -= 1;
+        Request r;
+        for (int i = 0; i < 3; i++) { r.origin[i] = cpu_.origin[i]; r.num_slices[i] = cpu_.num_loaded_slices[i]; }
+        r.axis = axis; r.new_position = cpu_;
+        queue_.push_back(r);
+    }
+    void request_move_towards(const int desired_center[3]) {                                                // :351-367: one request, X before Y before Z
+        int cur[3]; cpu_.render_offset(root_chunks_, cur);
+        for (int axis = 0; axis < 3; axis++) {
+            const int delta = desired_center[axis] - cur[axis];
+            if (delta > constants::SLICE_SIZE) { request_increase(axis); return; }
+            if (-delta > constants::SLICE_SIZE) { request_decrease(axis); return; }
+        }
+    }
+    void get_render_offset(int out[3]) const { gpu_.render_offset(root_chunks_, out); }                    // :288-290
+    size_t pending() const { return queue_.size(); }
+    // :277-286 — consume at most one request: one slab per frame
+    bool setup_next_request(ChunkStorage& world, VxrtHandle* h) {
+        if (queue_.empty()) return false;
+        const Request req = queue_.front();
+        queue_.erase(queue_.begin());
+        const int a = req.axis;
+        long start[3]; int shape[3];
+        for (int i = 0; i < 3; i++) { start[i] = req.origin[i] * constants::CHUNK_SIZE + (long)req.num_slices[i] * constants::SLICE_SIZE; shape[i] = window_[i]; }
+        shape[a] = constants::SLICE_SIZE;
+        const size_t n = (size_t)shape[0] * shape[1] * shape[2];
+        slab_m_.assign(n, 0u); slab_f_.assign(n, 0);
+        bool have_f = true;
+        // slab texel (x, y, z) <- world voxel start + ((x, y, z) - 16 * num_slices) mod N on the off axes, start + (x, y, z) on `a`
+        int shift[3];
+        for (int i = 0; i < 3; i++) shift[i] = i == a ? 0 : (req.num_slices[i] * constants::SLICE_SIZE) % window_[i];
+        auto fdiv64 = [](long v) { return v >= 0 ? v / 64 : -((-v + 63) / 64); };
+        for (int z = 0; z < shape[2]; z++) for (int y = 0; y < shape[1]; y++) {
+            const long wy = start[1] + ((y - shift[1]) % shape[1] + shape[1]) % shape[1], wz = start[2] + ((z - shift[2]) % shape[2] + shape[2]) % shape[2];
+            const long cy = fdiv64(wy), cz = fdiv64(wz);
+            for (int x = 0; x < shape[0];) {
+                const long wx = start[0] + ((x - shift[0]) % shape[0] + shape[0]) % shape[0];
+                const long cx = fdiv64(wx);
+                // a run along x inside one chunk and before the rotation wraps
+                int run = (int)((cx + 1) * 64 - wx);
+                const int until_wrap = shift[0] > x ? shift[0] - x : shape[0] - x;
+                if (run > until_wrap) run = until_wrap;
+                if (run > shape[0] - x) run = shape[0] - x;
+                PackedChunkData& c = world.borrow_packed_chunk_data(ChunkStorage::Coord(cx, cy, cz));
+                const size_t src = (size_t)((wz - cz * 64) * 64 + (wy - cy * 64)) * 64 + (size_t)(wx - cx * 64);
+                const size_t dst = ((size_t)z * shape[1] + y) * shape[0] + x;
+                std::memcpy(&slab_m_[dst], &c.materials[src], (size_t)run * sizeof(uint32_t));
+                if (c.minefield.empty()) have_f = false; else std::memcpy(&slab_f_[dst], &c.minefield[src], (size_t)run);
+                x += run;
+            }
+        }
+        const int offset = (req.num_slices[a] % slices_per_axis_[a]) * constants::SLICE_SIZE;             // :201-207
+        check(h, vxrt_upload_slice(h, a, offset, slab_m_.data(), have_f ? slab_f_.data() : nullptr));
+        gpu_ = req.new_position;
+        return true;
+    }
+  private:
+    int window_[3], root_chunks_[3], slices_per_axis_[3];
+    Position cpu_, gpu_;
+    std::vector<Request> queue_;
+    std::vector<uint32_t> slab_m_;
+    std::vector<uint8_t> slab_f_;
+};
+
 struct RenderOptions {                        // what constants.rs fixes at compile time
     int width = constants::WINDOW_WIDTH, height = constants::WINDOW_HEIGHT;
     int nx = constants::ROOT_BLOCK_SIZE, ny = constants::ROOT_BLOCK_SIZE, nz = constants::ROOT_BLOCK_SIZE;
     int mode = VXRT_MODE_FULL;
     uint32_t flags = VXRT_FLAG_DENOISE | VXRT_FLAG_FINALIZE;
     int device = 0;
+    bool streaming = false;                   // pipeline.rs:174-189: the window follows the camera, one 16-voxel slab per frame
 };
 
 // src/render/pipeline/pipeline.rs: Pipeline::new (:36-76) + draw_frame (:134-255) over the ABI
@@ -132,6 +232,7 @@ class Pipeline {
             PackedChunkData& c = world.borrow_packed_chunk_data(ChunkStorage::Coord(cx - o.nx / 128, cy - o.ny / 128, cz - o.nz / 128));
             check(h_, vxrt_upload_chunk(h_, cx, cy, cz, c.materials.data(), c.minefield.empty() ? nullptr : c.minefield.data()));
         }
+        if (o.streaming) tum_.reset(new TerrainUploadManager(o.nx, o.ny, o.nz));
         frame_.resize((size_t)o.width * o.height * 4);
         check(h_, vxrt_host_register(h_, frame_.data(), frame_.size()));
         std::memset(&uniform_data_, 0, sizeof uniform_data_);
@@ -143,6 +244,12 @@ class Pipeline {
     // pipeline.rs:191-235: fill the uniform block, submit, "present" (= read back into frame())
     void draw_frame(Game& game) {
         const Camera& cam = game.borrow_camera();
+        if (tum_) {                                                                                  // pipeline.rs:174-189 (y pinned to 0 there)
+            const int want[3] = {(int)cam.origin[0], 0, (int)cam.origin[2]};
+            tum_->request_move_towards(want);
+            tum_->setup_next_request(game.borrow_world_mut(), h_);
+            tum_->get_render_offset(render_offset_);
+        }
         const TripleEulerVector t = compute_triple_euler_vector(cam.heading, cam.pitch);
         VxrtFrameParams& u = uniform_data_;
         for (int i = 0; i < 3; i++) {
@@ -174,11 +281,13 @@ class Pipeline {
     VxrtFrameStats stats() { VxrtFrameStats s{}; check(h_, vxrt_frame_stats(h_, &s)); return s; }
     VxrtHandle* handle() { return h_; }
     const RenderOptions& options() const { return opt_; }
+    const int* render_offset() const { return render_offset_; }
   private:
     RenderOptions opt_;
     VxrtHandle* h_ = nullptr;
     VxrtFrameParams uniform_data_;
     int render_offset_[3] = {0, 0, 0};
+    std::unique_ptr<TerrainUploadManager> tum_;
     std::vector<uint8_t> frame_;
 };
 

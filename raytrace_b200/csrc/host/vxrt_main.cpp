@@ -4,6 +4,9 @@
 //
 //   vxrt_main --world words.u32 --dims NX NY NZ --noise noise.rgba [--size W H] [--frames N] [--mode 0|1|2]
 //             [--camera x y z heading pitch sun] [--hold forward] [--dt 0.016] [--out frame.ppm] [--block block.bin]
+//             [--world-dims WX WY WZ]  the file holds a world larger than the window (chunks around it)
+//             [--stream]               the window follows the camera (TerrainUploadManager, pipeline.rs:174-189)
+//             [--dump-world file]      materials (u32) then occupancy field (u8) of the device window after the last frame
 #include <chrono>
 #include <cstdlib>
 #include <fstream>
@@ -22,8 +25,8 @@ static std::vector<char> slurp(const std::string& path) {
 int main(int argc, char** argv) {
     try {
         RenderOptions o;
-        std::string world_path, noise_path, out_path, block_path, hold;
-        int frames = 1;
+        std::string world_path, noise_path, out_path, block_path, hold, dump_path;
+        int frames = 1, wd[3] = {0, 0, 0};
         float dt = 0.016f;
         std::unique_ptr<Game> game(new Game());
         for (int i = 1; i < argc; i++) {
@@ -38,6 +41,9 @@ int main(int argc, char** argv) {
             else if (a == "--dt") { need(1); dt = (float)std::atof(argv[++i]); }
             else if (a == "--mode") { need(1); o.mode = std::atoi(argv[++i]); }
             else if (a == "--dims") { need(3); o.nx = std::atoi(argv[++i]); o.ny = std::atoi(argv[++i]); o.nz = std::atoi(argv[++i]); }
+            else if (a == "--world-dims") { need(3); wd[0] = std::atoi(argv[++i]); wd[1] = std::atoi(argv[++i]); wd[2] = std::atoi(argv[++i]); }
+            else if (a == "--stream") o.streaming = true;
+            else if (a == "--dump-world") { need(1); dump_path = argv[++i]; }
             else if (a == "--size") { need(2); o.width = std::atoi(argv[++i]); o.height = std::atoi(argv[++i]); }
             else if (a == "--camera") {
                 need(6);
@@ -47,9 +53,10 @@ int main(int argc, char** argv) {
         }
         if (world_path.empty() || noise_path.empty()) throw std::runtime_error("--world and --noise are required");
         const std::vector<char> words = slurp(world_path), noise = slurp(noise_path);
-        if (words.size() != (size_t)o.nx * o.ny * o.nz * 4) throw std::runtime_error("world file size does not match --dims");
+        if (!wd[0]) { wd[0] = o.nx; wd[1] = o.ny; wd[2] = o.nz; }
+        if (words.size() != (size_t)wd[0] * wd[1] * wd[2] * 4) throw std::runtime_error("world file size does not match --dims / --world-dims");
         if (noise.size() != (size_t)constants::BLUE_NOISE_SIZE) throw std::runtime_error("noise file must be 512*512*4 bytes");
-        game->borrow_world_mut().store_window(reinterpret_cast<const uint32_t*>(words.data()), o.nx, o.ny, o.nz);
+        game->borrow_world_mut().store_window(reinterpret_cast<const uint32_t*>(words.data()), wd[0], wd[1], wd[2]);
         if (!hold.empty()) game->hold(hold, true);
 
         std::printf("Creating renderer (and world.)\n");
@@ -73,6 +80,13 @@ int main(int argc, char** argv) {
             f << "P6\n" << o.width << " " << o.height << "\n255\n";
             const std::vector<uint8_t>& px = pipeline->frame();
             for (size_t p = 0; p < px.size(); p += 4) f.write(reinterpret_cast<const char*>(&px[p]), 3);
+        }
+        if (!dump_path.empty()) {
+            std::vector<uint32_t> m((size_t)o.nx * o.ny * o.nz); std::vector<uint8_t> f(m.size());
+            check(pipeline->handle(), vxrt_read_world(pipeline->handle(), m.data(), f.data()));
+            std::ofstream df(dump_path, std::ios::binary);
+            df.write(reinterpret_cast<const char*>(m.data()), (std::streamsize)(m.size() * 4));
+            df.write(reinterpret_cast<const char*>(f.data()), (std::streamsize)f.size());
         }
         if (!block_path.empty()) {
             std::ofstream f(block_path, std::ios::binary);

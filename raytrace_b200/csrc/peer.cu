@@ -267,6 +267,10 @@ int vxrt_peer_error_word(VxrtHandle* h, uint32_t* out) {
     return VXRT_OK;
 }
 
+void vxrt_peer_clear_error(VxrtHandle* h) {
+    if (h->peer_on) cudaMemsetAsync(h->d_peer_flags + F_ERROR, 0, 4, h->stream);
+}
+
 extern "C" {
 
 int vxrt_peer_export(VxrtHandle* h, void* blob, size_t nbytes) {

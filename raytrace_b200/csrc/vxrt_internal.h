@@ -93,6 +93,7 @@ struct VxrtHandle {
     std::vector<uint8_t> h_noise;        // host copy: the seed texel is read on the host (raytrace.comp:298-303)
     uint32_t* d_dirty;                   // one flag per 64^3 chunk
     void* d_edits; size_t edits_cap;
+    void* d_edit_table = nullptr; size_t edit_table_slots = 0;     // last-wins resolution of duplicate voxels in an edit list (world.cu)
     // vxrt_apply_edits stages the caller's list through two page-locked buffers, so it returns without waiting for the
     // frames still queued on the stream (ev_edits[i]: the copy out of buffer i has been issued and completed)
     void* h_edits[2] = {nullptr, nullptr}; size_t h_edits_cap = 0; cudaEvent_t ev_edits[2] = {nullptr, nullptr}; int edit_slot = 0;
@@ -128,6 +129,7 @@ VxrtPeerTail vxrt_peer_finalize_tail(VxrtHandle* h);
 uchar4* vxrt_peer_output(VxrtHandle* h, int out_idx);
 int vxrt_peer_end_frame(VxrtHandle* h);
 int vxrt_peer_error_word(VxrtHandle* h, uint32_t* out);
+void vxrt_peer_clear_error(VxrtHandle* h);
 
 // module preload (cudaFuncGetAttributes on every kernel of a file)
 cudaError_t vxrt_preload_trace(); cudaError_t vxrt_preload_trace_fast(); cudaError_t vxrt_preload_post();
@@ -150,5 +152,7 @@ cudaError_t vxrt_launch_row_cost(const uint32_t* steps, const uint8_t* rays, con
 cudaError_t vxrt_launch_build_minefield(uint32_t* materials, uint8_t* minefield, int nx, int ny, int nz,
                                         const uint32_t* dirty /*NULL = all chunks*/, cudaStream_t s);
 cudaError_t vxrt_launch_apply_edits(uint32_t* materials, uint32_t* dirty, const VxrtEdit* d_edits, size_t n,
-                                    int nx, int ny, int nz, cudaStream_t s);
+                                    int nx, int ny, int nz, void* table /* 12 bytes per slot */, size_t table_slots /* pow2 >= 4n */, cudaStream_t s);
+cudaError_t vxrt_launch_compare_chunk(const uint8_t* minefield, const uint8_t* d_stored, int nx, int ny, int cx, int cy, int cz,
+                                      unsigned long long* d_out /* [0] mismatching bytes, [1] first offset */, cudaStream_t s);
 cudaError_t vxrt_launch_generate(uint32_t* materials, int nx, int ny, int nz, int kind, uint32_t seed, cudaStream_t s);

@@ -106,15 +106,57 @@ __global__ void __launch_bounds__(512) k_build_minefield(uint32_t* __restrict__ 
     }
 }
 
-// world coordinate -> window texel: (w + N/2) mod N (raytrace.comp:105-106)
+// Stored-chunk validation (chunk_storage.rs:56-68 reads materials || minefield from a file): the 64^3 occupancy bytes a file
+// carries against the ones k_build_minefield derives from the window's words.  One thread per 4 voxels; mismatching bytes are
+// counted, the first mismatching texel offset (in the chunk) is kept.
+__global__ void __launch_bounds__(256) k_compare_chunk(const uint8_t* __restrict__ minefield, const uint8_t* __restrict__ stored,
+                                                       int nx, int ny, int cx, int cy, int cz, unsigned long long* __restrict__ out) {
+    const int q = blockIdx.x * 256 + threadIdx.x;              // 65536 threads: q = z*1024 + y*16 + x4
+    const int x4 = q & 15, y = (q >> 4) & 63, z = q >> 10;
+    const size_t gi = ((size_t)(cz * 64 + z) * ny + cy * 64 + y) * nx + cx * 64 + x4 * 4;
+    const uint32_t a = *reinterpret_cast<const uint32_t*>(minefield + gi), b = __ldg(reinterpret_cast<const uint32_t*>(stored) + q);
+    uint32_t bad = 0, first = 4;
+#pragma unroll
+    for (int k = 3; k >= 0; k--) if (((a >> (8 * k)) & 0xFFu) != ((b >> (8 * k)) & 0xFFu)) { bad++; first = k; }
+    if (bad) { atomicAdd(out, (unsigned long long)bad); atomicMin(out + 1, (unsigned long long)(q * 4 + first)); }
+}
+
+// Voxel edits.  world coordinate -> window texel: (w + N/2) mod N (raytrace.comp:105-106).  A list may name a voxel more than
+// once; the reference's set_block (chunk.rs:115-117) applied in list order makes the LAST entry win, and every replica of a
+// multi-GPU run must resolve it the same way.  Two passes over an open-addressing table keyed by the texel offset: pass 1
+// leaves the highest list index of each voxel in the table (atomicMax), pass 2 lets exactly that entry write.
+__device__ __forceinline__ unsigned long long edit_key(const VxrtEdit& e, int nx, int ny, int nz) {
+    const uint32_t x = (uint32_t)(e.x + nx / 2) & (uint32_t)(nx - 1), y = (uint32_t)(e.y + ny / 2) & (uint32_t)(ny - 1),
+                   z = (uint32_t)(e.z + nz / 2) & (uint32_t)(nz - 1);
+    return ((unsigned long long)z * ny + y) * nx + x;
+}
+__device__ __forceinline__ uint32_t edit_slot(unsigned long long key, uint32_t mask) {
+    key ^= key >> 29; key *= 0xBF58476D1CE4E5B9ull; key ^= key >> 32;
+    return (uint32_t)key & mask;
+}
+__global__ void k_claim_edits(const VxrtEdit* __restrict__ edits, size_t n, int nx, int ny, int nz,
+                              unsigned long long* __restrict__ keys, uint32_t* __restrict__ winner, uint32_t mask) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const unsigned long long key = edit_key(edits[i], nx, ny, nz) + 1ull;       // 0 = empty slot
+    for (uint32_t h = edit_slot(key, mask);; h = (h + 1u) & mask) {
+        const unsigned long long prev = atomicCAS(keys + h, 0ull, key);
+        if (prev == 0ull || prev == key) { atomicMax(winner + h, (uint32_t)i + 1u); return; }
+    }
+}
 __global__ void k_apply_edits(uint32_t* __restrict__ materials, uint32_t* __restrict__ dirty, const VxrtEdit* __restrict__ edits,
-                              size_t n, int nx, int ny, int nz) {
+                              size_t n, int nx, int ny, int nz, const unsigned long long* __restrict__ keys,
+                              const uint32_t* __restrict__ winner, uint32_t mask) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const VxrtEdit e = edits[i];
-    const uint32_t x = (uint32_t)(e.x + nx / 2) & (uint32_t)(nx - 1), y = (uint32_t)(e.y + ny / 2) & (uint32_t)(ny - 1),
-                   z = (uint32_t)(e.z + nz / 2) & (uint32_t)(nz - 1);
-    materials[((size_t)z * ny + y) * nx + x] = e.word;
+    const unsigned long long off = edit_key(e, nx, ny, nz), key = off + 1ull;
+    uint32_t h = edit_slot(key, mask);
+    while (keys[h] != key) h = (h + 1u) & mask;                               // present: pass 1 put it there
+    if (winner[h] != (uint32_t)i + 1u) return;                                // a later entry of the list names this voxel
+    materials[off] = e.word;
+    const uint32_t x = (uint32_t)(off % (unsigned long long)nx), y = (uint32_t)((off / (unsigned long long)nx) % (unsigned long long)ny),
+                   z = (uint32_t)(off / ((unsigned long long)nx * ny));
     dirty[((z >> 6) * (ny >> 6) + (y >> 6)) * (nx >> 6) + (x >> 6)] = 1u;
 }
 
@@ -197,7 +239,13 @@ __global__ void __launch_bounds__(256) k_generate(uint32_t* __restrict__ materia
 
 // see peer.cu: every kernel is loaded when a handle is created (a lazy load cannot complete under a spinning kernel)
 #define VXRT_PRELOAD(k) do { cudaFuncAttributes a_; cudaError_t e_ = cudaFuncGetAttributes(&a_, k); if (e_ != cudaSuccess) return e_; } while (0)
-cudaError_t vxrt_preload_world() { VXRT_PRELOAD(k_build_minefield); VXRT_PRELOAD(k_apply_edits); VXRT_PRELOAD(k_generate); return cudaSuccess; }
+cudaError_t vxrt_preload_world() { VXRT_PRELOAD(k_build_minefield); VXRT_PRELOAD(k_claim_edits); VXRT_PRELOAD(k_apply_edits); VXRT_PRELOAD(k_generate); VXRT_PRELOAD(k_compare_chunk); return cudaSuccess; }
+
+cudaError_t vxrt_launch_compare_chunk(const uint8_t* minefield, const uint8_t* d_stored, int nx, int ny, int cx, int cy, int cz,
+                                      unsigned long long* d_out, cudaStream_t s) {
+    k_compare_chunk<<<256, 256, 0, s>>>(minefield, d_stored, nx, ny, cx, cy, cz, d_out);
+    return cudaGetLastError();
+}
 
 cudaError_t vxrt_launch_build_minefield(uint32_t* materials, uint8_t* minefield, int nx, int ny, int nz,
                                         const uint32_t* dirty, cudaStream_t s) {
@@ -207,9 +255,16 @@ cudaError_t vxrt_launch_build_minefield(uint32_t* materials, uint8_t* minefield,
 }
 
 cudaError_t vxrt_launch_apply_edits(uint32_t* materials, uint32_t* dirty, const VxrtEdit* d_edits, size_t n,
-                                    int nx, int ny, int nz, cudaStream_t s) {
+                                    int nx, int ny, int nz, void* table, size_t table_slots, cudaStream_t s) {
     if (n == 0) return cudaSuccess;
-    k_apply_edits<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(materials, dirty, d_edits, n, nx, ny, nz);
+    // table: table_slots (a power of two >= 4 n) keys of 8 bytes, then as many 4-byte winners
+    unsigned long long* keys = (unsigned long long*)table;
+    uint32_t* winner = (uint32_t*)(keys + table_slots);
+    cudaError_t e = cudaMemsetAsync(table, 0, table_slots * 12, s);
+    if (e != cudaSuccess) return e;
+    const unsigned blocks = (unsigned)((n + 255) / 256);
+    k_claim_edits<<<blocks, 256, 0, s>>>(d_edits, n, nx, ny, nz, keys, winner, (uint32_t)(table_slots - 1));
+    k_apply_edits<<<blocks, 256, 0, s>>>(materials, dirty, d_edits, n, nx, ny, nz, keys, winner, (uint32_t)(table_slots - 1));
     return cudaGetLastError();
 }
 

@@ -75,3 +75,37 @@ def test_disk_chunk_storage(orc, tmp_path):
     got = st2.borrow_packed_chunk_data((-1, 0, 2))
     assert np.array_equal(got.materials, m) and np.array_equal(got.minefield, f)
     assert not st2.borrow_packed_chunk_data((9, 9, 9)).materials.any()
+
+
+@pytest.mark.gpu
+def test_stored_chunks_feed_the_device_and_validate(orc, tmp_path):
+    """SURVEY 8(f)2 end to end on the GPU: chunks written in the reference's file format (chunk_storage.rs:37-68), read back
+    through DiskChunkStorage -> vxrt_chunk_decode -> vxrt_upload_chunk(materials, NULL): the occupancy field the device builds
+    from the stored words equals the stored one (vxrt_validate_chunk, compared on the device), a corrupted file is caught with
+    the offset of the damage, and the whole window equals the world the files were cut from."""
+    import raytrace_b200 as R
+    from raytrace_b200 import scenes
+    from raytrace_b200.world import DiskChunkStorage
+    dims, kind, seed = scenes.WORLDS["c1"]
+    m = orc.generate_world(*dims, kind, seed)
+    m, f = orc.build_minefield(m)
+    src = R.ChunkStorage.from_window(m, f)
+    disk = DiskChunkStorage(str(tmp_path))
+    for coord, data in src.chunks.items():
+        disk.save(coord, data)
+    fresh = DiskChunkStorage(str(tmp_path))                     # nothing in memory: every chunk comes off the disk
+    n = dims[0] // 64
+    with R.Renderer(64, 64, dims, 0, 0) as r:
+        for cz in range(n):
+            for cy in range(n):
+                for cx in range(n):
+                    data = fresh.borrow_packed_chunk_data((cx - n // 2, cy - n // 2, cz - n // 2))
+                    r.upload_chunk(cx, cy, cz, data.materials, None)       # occupancy built on the device
+                    assert r.validate_chunk(cx, cy, cz, data.minefield) == (0, -1)
+        gm, gf = r.read_world()
+        assert np.array_equal(gm, m) and np.array_equal(gf, f)
+        bad = fresh.borrow_packed_chunk_data((0, 0, 0)).minefield.copy()
+        bad[5, 6, 7] ^= 1; bad[40, 1, 2] ^= 3
+        assert r.validate_chunk(n // 2, n // 2, n // 2, bad) == (2, (5 * 64 + 6) * 64 + 7)
+        with pytest.raises(R.VxrtError):
+            r.validate_chunk(n, 0, 0, bad)

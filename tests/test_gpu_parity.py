@@ -603,3 +603,25 @@ def test_second_bounce_handoff_is_invisible(orc, world, noise, scene, width, hei
             assert np.array_equal(hand.read_buffer(N.BUF_DEPTH), ref.depth) and np.array_equal(hand.read_buffer(N.BUF_NORMAL), ref.normal)
             d = np.abs(hand.read_buffer(N.BUF_LIGHTING).astype(np.int64) - ref.lighting.astype(np.int64)).max()
             assert d <= C16_TOL, d
+
+
+def test_duplicate_edits_last_entry_wins(orc, world):
+    """An edit list that names voxels several times: set_block applied in list order (chunk.rs:115-117) leaves the LAST word;
+    k_apply_edits resolves it the same way on every run (one thread per edit used to race)."""
+    import raytrace_b200 as R
+    from raytrace_b200 import scenes
+    dims = scenes.WORLDS["c1"][0]
+    m, f = world("c1")
+    rng = np.random.default_rng(3)
+    base = orc.generate_edits(3000, *dims, 9, 0)
+    pick = rng.integers(0, 200, size=9000)                         # 200 voxels named ~45 times each, interleaved
+    e = base[pick].copy()
+    e[:, 3] = rng.integers(0, 2, size=len(e)) * 0xCD9B3
+    e = np.concatenate([base, e, base[:50]]).astype(np.int32)
+    want = m.copy(); orc.apply_edits(want, e)                      # sequential, list order
+    want, wf = orc.build_minefield(want)
+    for _ in range(3):
+        with R.Renderer(64, 64, dims, 0, 0) as r:
+            r.upload_world(m, f); r.apply_edits(e)
+            gm, gf = r.read_world()
+            assert np.array_equal(gm, want) and np.array_equal(gf, wf)

@@ -88,3 +88,38 @@ def test_streaming_pipeline_matches_oracle(orc, noise):
         assert offsets[-1][0] >= 48 and offsets[-1][1] == 0     # y is pinned (pipeline.rs:174-178); z follows the camera too
     finally:
         pipe.close()
+
+
+@pytest.mark.gpu
+def test_cpp_host_streams_across_a_region_boundary(orc, noise, tmp_path):
+    """The compiled host (csrc/host/vxrt_host.hpp): Pipeline::draw_frame drives its own TerrainUploadManager as
+    pipeline.rs:174-189 does.  The headless driver flies +x for 12 frames over a world twice as wide as the window, one slab
+    per frame, through a region roll-over; the device window must equal expected_window for the render offset the driver
+    put into its last uniform block, occupancy field included (built on the device: the chunks carry none)."""
+    import os, subprocess
+    import raytrace_b200 as R
+    from raytrace_b200.terrain_upload import expected_window
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "raytrace_b200", "vxrt_main")
+    assert os.path.exists(exe), "vxrt_main not built (raytrace_b200/build.py)"
+    wd, win = (256, 128, 128), (128, 128, 128)
+    m = orc.generate_world(*wd, 0, 11)
+    (tmp_path / "w.u32").write_bytes(np.ascontiguousarray(m).tobytes())
+    (tmp_path / "n.rgba").write_bytes(np.ascontiguousarray(noise).tobytes())
+    cmd = [exe, "--world", str(tmp_path / "w.u32"), "--world-dims", *map(str, wd), "--dims", *map(str, win), "--noise", str(tmp_path / "n.rgba"),
+           "--size", "96", "64", "--frames", "12", "--hold", "right", "--dt", "0.4", "--mode", "2", "--stream",
+           "--camera", "0.5", "-60.0", "45.25", "1.5707963", "-0.3", "0.7",
+           "--block", str(tmp_path / "b.bin"), "--dump-world", str(tmp_path / "d.bin")]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=180)
+    assert p.returncode == 0, p.stderr
+    blk = np.frombuffer((tmp_path / "b.bin").read_bytes(), np.uint8)
+    lr = tuple(int(v) for v in blk[160:172].view(np.int32))
+    assert lr[0] >= 128 + 16 and lr[1] == 0, lr                     # past the first region (8 slabs of 16) on x; y pinned
+    raw = (tmp_path / "d.bin").read_bytes()
+    V = win[0] * win[1] * win[2]
+    gm = np.frombuffer(raw[:4 * V], np.uint32).reshape(win[2], win[1], win[0])
+    gf = np.frombuffer(raw[4 * V:], np.uint8).reshape(win[2], win[1], win[0])
+    st = R.ChunkStorage.from_window(m)                              # the same chunk cut as ChunkStorage::store_window
+    em, _ = expected_window(st, win, lr)
+    assert np.array_equal(gm, em)
+    _, ef = orc.build_minefield(em)                                 # pack_into per 64^3 chunk: window chunks are world chunks
+    assert np.array_equal(gf, ef)
