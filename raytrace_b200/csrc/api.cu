@@ -485,6 +485,7 @@ void vxrt_destroy(VxrtHandle* h) {
     }
     for (int i = 0; i < 2; i++) if (h->field_tex[i] && !h->world_owner) cudaDestroyTextureObject(h->field_tex[i]);
     if (h->field_arr && !h->world_owner) cudaFreeArray(h->field_arr);
+    for (int i = 0; i < 2; i++) { if (h->graphs[i].exec) cudaGraphExecDestroy(h->graphs[i].exec); if (h->graphs[i].graph) cudaGraphDestroy(h->graphs[i].graph); }
     if (h->ev_accum) cudaEventDestroy(h->ev_accum);
     if (h->ev_world) cudaEventDestroy(h->ev_world);
     void* ptrs[] = {h->d_materials, h->d_minefield, h->d_noise, h->d_lut, h->d_dirty, h->d_edits, h->d_edit_table, h->d_lighting, h->d_pong,
@@ -725,6 +726,97 @@ int vxrt_reset_history(VxrtHandle* h) {
     return VXRT_OK;
 }
 
+// The device work of one frame on the handle's stream: counter reset, trace pass, [reprojection], six denoise passes,
+// finalize, with the four events vxrt_frame_stats reads.  Issued directly, or once into a stream capture (capturing: the host-side
+// read-back wait is the caller's, events are recorded as graph nodes).
+static int issue_frame(VxrtHandle* h, TraceParams& P, const VxrtFrameParams& f, bool capturing) {
+    int prc;
+    const unsigned evf = capturing ? cudaEventRecordExternal : cudaEventRecordDefault;
+    CU(cudaMemsetAsync(h->d_counters, 0, 8 * sizeof(unsigned long long), h->stream));
+    CU(cudaEventRecordWithFlags(h->ev[0], h->stream, evf));
+    if (!h->peer_on) {
+        CU(vxrt_launch_trace(P, h->stream));
+    } else {
+        // peer.cu: the rows a neighbour's denoise needs are traced first and stored into its images while this
+        // band's interior is still being traced
+        int32_t iv[2 * VXRT_PEER_MAX_LINKS];
+        // measured at N=2 (profiles/r1_m): splitting the trace pass into boundary + interior launches costs more in partial
+        // waves than the earlier push wins, so the whole band is traced first; the split stays behind a switch
+        static const bool boundary_first = getenv("VXRT_PEER_BOUNDARY_FIRST") != nullptr;
+        const int n = boundary_first ? vxrt_peer_boundary_rows(h, iv) : 0;
+        for (int i = 0; i < n; i++) { P.row0 = iv[2 * i]; P.row1 = iv[2 * i + 1]; CU(vxrt_launch_trace(P, h->stream)); }
+        if (n && (prc = vxrt_peer_push_halo(h))) return prc;
+        int at = h->row0;
+        for (int i = 0; i <= n; i++) {
+            const int gap_end = i < n ? iv[2 * i] : h->row1;
+            if (gap_end > at) { P.row0 = at; P.row1 = gap_end; CU(vxrt_launch_trace(P, h->stream)); }
+            if (i < n) at = iv[2 * i + 1];
+        }
+        if (!n && (prc = vxrt_peer_push_halo(h))) return prc;
+    }
+    CU(cudaEventRecordWithFlags(h->ev[1], h->stream, evf));
+    if (h->d_accum && (prc = accum_written(h))) return prc;
+    if (h->peer_on && (prc = vxrt_peer_wait_halo(h))) return prc;
+    if (h->d_lighting_raw)
+        CU(cudaMemcpyAsync(h->d_lighting_raw, h->d_lighting, pixels(h) * 8, cudaMemcpyDeviceToDevice, h->stream));
+    if (h->d_hist[0]) {                                                  // temporal.cu; timed with the denoise passes
+        ReprojectParams R;
+        memset(&R, 0, sizeof R);
+        R.oox = f.old_origin[0]; R.ooy = f.old_origin[1]; R.ooz = f.old_origin[2];
+        R.c0x = f.old_transform_c0[0]; R.c0y = f.old_transform_c0[1]; R.c0z = f.old_transform_c0[2];
+        R.c1x = f.old_transform_c1[0]; R.c1y = f.old_transform_c1[1]; R.c1z = f.old_transform_c1[2];
+        R.c2x = f.old_transform_c2[0]; R.c2y = f.old_transform_c2[1]; R.c2z = f.old_transform_c2[2];
+        R.width = h->cfg.width; R.height = h->cfg.height;
+        R.lighting = h->d_lighting; R.completed = h->d_completed;
+        R.hit_pos_cur = h->d_hit_pos[h->hist_idx]; R.hit_pos_prev = h->d_hit_pos[h->hist_idx ^ 1];
+        R.hist_prev = h->d_hist[h->hist_idx ^ 1]; R.hist_cur = h->d_hist[h->hist_idx];
+        CU(vxrt_launch_reproject(R, h->stream));
+    }
+    bool fold = false;
+    if (h->cfg.flags & VXRT_FLAG_DENOISE) {
+        // pipeline.rs:98-115: even passes lighting -> pong, odd passes pong -> lighting.  A band shrinks
+        // by 3*size rows per pass towards [row0,row1) so that only valid rows are ever read.
+        // passes 2..6 follow a denoise launch directly: programmatic dependent launch (post.cu) lets a pass become
+        // resident while its predecessor drains
+        static const bool pdl = getenv("VXRT_NO_PDL") == nullptr;
+        static const bool want_fold = getenv("VXRT_FOLD") != nullptr;
+        // VXRT_FOLD=1: finalize.comp rides on the last pass (one launch, one grid tail and a read of the lighting image less).
+        // Measured on the B200 (r2_h, C2): six passes + finalize 0.1915 ms apart, 0.1938 ms folded - the last pass's tiles
+        // (128 x 128 pixels at dilation 16) finish later with the extra loads and the flipped-row stores than the 0.016 ms
+        // finalize grid costs on its own - so the separate launch stays the default.
+        fold = (h->cfg.flags & VXRT_FLAG_FINALIZE) && !h->peer_on && want_fold;
+        for (int k = 0; k < 6; k++) {
+            const int r0 = h->plan[2 + 2 * k], r1 = h->plan[3 + 2 * k];
+            const bool odd = (k & 1) != 0;
+            const int swap = (odd && (h->cfg.flags & VXRT_FLAG_PONG_SWAP)) ? 1 : 0;
+            VxrtFinalizeFold ff = {h->d_albedo, h->d_emission, h->d_fog, h->d_noise, h->d_output, h->row0, h->row1};
+            if (!capturing && k == 5 && fold && h->copy_pending[h->out_idx]) {            // the output image may still be on its way to the host
+                CU(cudaStreamWaitEvent(h->stream, h->ev_copy_done[h->out_idx], 0));
+                h->copy_pending[h->out_idx] = false;
+            }
+            CU(vxrt_launch_denoise(odd ? h->d_pong : h->d_lighting, odd ? h->d_lighting : h->d_pong, h->d_depth, h->d_normal,
+                                   h->cfg.width, h->cfg.height, kDenoiseSizes[k], swap, r0, r1, h->stream, k > 0 && pdl,
+                                   k == 5 && fold ? &ff : nullptr));
+        }
+    }
+    if (h->peer_on && (prc = vxrt_peer_after_denoise(h))) return prc;
+    CU(cudaEventRecordWithFlags(h->ev[2], h->stream, evf));
+    if (!capturing && h->copy_pending[h->out_idx]) {
+        CU(cudaStreamWaitEvent(h->stream, h->ev_copy_done[h->out_idx], 0));
+        h->copy_pending[h->out_idx] = false;
+    }
+    if ((h->cfg.flags & VXRT_FLAG_FINALIZE) && !fold) {
+        VxrtPeerTail tail;
+        if (h->peer_on) tail = vxrt_peer_finalize_tail(h);
+        CU(vxrt_launch_finalize(h->d_albedo, h->d_emission, h->d_fog, h->d_lighting, h->d_depth, h->d_noise,
+                                h->peer_on ? vxrt_peer_output(h, h->out_idx) : h->d_output,       // peer mode: straight into the root's image
+                                h->cfg.width, h->cfg.height, h->row0, h->row1, h->stream, h->peer_on ? &tail : nullptr));
+    }
+    if (h->peer_on && (prc = vxrt_peer_end_frame(h))) return prc;
+    CU(cudaEventRecordWithFlags(h->ev[3], h->stream, evf));
+    return VXRT_OK;
+}
+
 int vxrt_render_frame(VxrtHandle* h) {
     if (!h) return VXRT_ERR_INVALID;
     const VxrtHandle* wo = world_of(h);
@@ -800,89 +892,67 @@ int vxrt_render_frame(VxrtHandle* h) {
         h->world_seen = h->world_owner->world_version;
     }
     if (h->d_accum && (prc = accum_wait(h))) return prc;                // shared running sum: after the previous frame's trace pass
-    CU(cudaMemsetAsync(h->d_counters, 0, 8 * sizeof(unsigned long long), h->stream));
-    CU(cudaEventRecord(h->ev[0], h->stream));
-    if (!h->peer_on) {
-        CU(vxrt_launch_trace(P, h->stream));
-    } else {
-        // peer.cu: the rows a neighbour's denoise needs are traced first and stored into its images while this
-        // band's interior is still being traced
-        int32_t iv[2 * VXRT_PEER_MAX_LINKS];
-        // measured at N=2 (profiles/r1_m): splitting the trace pass into boundary + interior launches costs more in partial
-        // waves than the earlier push wins, so the whole band is traced first; the split stays behind a switch
-        static const bool boundary_first = getenv("VXRT_PEER_BOUNDARY_FIRST") != nullptr;
-        const int n = boundary_first ? vxrt_peer_boundary_rows(h, iv) : 0;
-        for (int i = 0; i < n; i++) { P.row0 = iv[2 * i]; P.row1 = iv[2 * i + 1]; CU(vxrt_launch_trace(P, h->stream)); }
-        if (n && (prc = vxrt_peer_push_halo(h))) return prc;
-        int at = h->row0;
-        for (int i = 0; i <= n; i++) {
-            const int gap_end = i < n ? iv[2 * i] : h->row1;
-            if (gap_end > at) { P.row0 = at; P.row1 = gap_end; CU(vxrt_launch_trace(P, h->stream)); }
-            if (i < n) at = iv[2 * i + 1];
+    // (8) one CUDA graph per output image replays the frame - counter memset, trace, six denoise passes, finalize, the four
+    // event records - with the trace node's parameters set per frame: one submission instead of ten.  Whatever orders the frame
+    // against the host or other streams stays outside: the world / running-sum waits above, the read-back wait below.
+    static const bool no_graph = getenv("VXRT_NO_GRAPH") != nullptr;
+    const bool shared_sum = h->d_accum && (h->accum_borrowed || !h->sharers.empty());
+    if (!no_graph && !h->graph_failed && !h->peer_on && !h->d_hist[0] && !shared_sum) {
+        if (h->copy_pending[h->out_idx]) {
+            CU(cudaStreamWaitEvent(h->stream, h->ev_copy_done[h->out_idx], 0));
+            h->copy_pending[h->out_idx] = false;
         }
-        if (!n && (prc = vxrt_peer_push_halo(h))) return prc;
-    }
-    CU(cudaEventRecord(h->ev[1], h->stream));
-    if (h->d_accum && (prc = accum_written(h))) return prc;
-    if (h->peer_on && (prc = vxrt_peer_wait_halo(h))) return prc;
-    if (h->d_lighting_raw)
-        CU(cudaMemcpyAsync(h->d_lighting_raw, h->d_lighting, pixels(h) * 8, cudaMemcpyDeviceToDevice, h->stream));
-    if (h->d_accum) accum_keeper(h)->frames_accumulated++;
-    if (h->d_hist[0]) {                                                  // temporal.cu; timed with the denoise passes
-        ReprojectParams R;
-        memset(&R, 0, sizeof R);
-        R.oox = f.old_origin[0]; R.ooy = f.old_origin[1]; R.ooz = f.old_origin[2];
-        R.c0x = f.old_transform_c0[0]; R.c0y = f.old_transform_c0[1]; R.c0z = f.old_transform_c0[2];
-        R.c1x = f.old_transform_c1[0]; R.c1y = f.old_transform_c1[1]; R.c1z = f.old_transform_c1[2];
-        R.c2x = f.old_transform_c2[0]; R.c2y = f.old_transform_c2[1]; R.c2z = f.old_transform_c2[2];
-        R.width = h->cfg.width; R.height = h->cfg.height;
-        R.lighting = h->d_lighting; R.completed = h->d_completed;
-        R.hit_pos_cur = h->d_hit_pos[h->hist_idx]; R.hit_pos_prev = h->d_hit_pos[h->hist_idx ^ 1];
-        R.hist_prev = h->d_hist[h->hist_idx ^ 1]; R.hist_cur = h->d_hist[h->hist_idx];
-        CU(vxrt_launch_reproject(R, h->stream));
-    }
-    bool fold = false;
-    if (h->cfg.flags & VXRT_FLAG_DENOISE) {
-        // pipeline.rs:98-115: even passes lighting -> pong, odd passes pong -> lighting.  A band shrinks
-        // by 3*size rows per pass towards [row0,row1) so that only valid rows are ever read.
-        // passes 2..6 follow a denoise launch directly: programmatic dependent launch (post.cu) lets a pass become
-        // resident while its predecessor drains
-        static const bool pdl = getenv("VXRT_NO_PDL") == nullptr;
-        static const bool want_fold = getenv("VXRT_FOLD") != nullptr;
-        // VXRT_FOLD=1: finalize.comp rides on the last pass (one launch, one grid tail and a read of the lighting image less).
-        // Measured on the B200 (r2_h, C2): six passes + finalize 0.1915 ms apart, 0.1938 ms folded - the last pass's tiles
-        // (128 x 128 pixels at dilation 16) finish later with the extra loads and the flipped-row stores than the 0.016 ms
-        // finalize grid costs on its own - so the separate launch stays the default.
-        fold = (h->cfg.flags & VXRT_FLAG_FINALIZE) && !h->peer_on && want_fold;
-        for (int k = 0; k < 6; k++) {
-            const int r0 = h->plan[2 + 2 * k], r1 = h->plan[3 + 2 * k];
-            const bool odd = (k & 1) != 0;
-            const int swap = (odd && (h->cfg.flags & VXRT_FLAG_PONG_SWAP)) ? 1 : 0;
-            VxrtFinalizeFold ff = {h->d_albedo, h->d_emission, h->d_fog, h->d_noise, h->d_output, h->row0, h->row1};
-            if (k == 5 && fold && h->copy_pending[h->out_idx]) {            // the output image may still be on its way to the host
-                CU(cudaStreamWaitEvent(h->stream, h->ev_copy_done[h->out_idx], 0));
-                h->copy_pending[h->out_idx] = false;
+        VxrtHandle::FrameGraph& g = h->graphs[h->out_idx];
+        dim3 grid, block;
+        const void* func = vxrt_trace_kernel(P, &grid, &block);
+        const bool same = g.exec && g.func == func && g.grid.x == grid.x && g.grid.y == grid.y && g.block.x == block.x;
+        if (!same) {
+            if (g.exec) { cudaGraphExecDestroy(g.exec); g.exec = nullptr; }
+            if (g.graph) { cudaGraphDestroy(g.graph); g.graph = nullptr; }   // (kept while its exec lives: the node handle names a node of it)
+            cudaGraph_t graph = nullptr;
+            cudaError_t e = cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal);
+            int brc = VXRT_OK;
+            if (e == cudaSuccess) {
+                brc = issue_frame(h, P, f, true);
+                e = cudaStreamEndCapture(h->stream, &graph);
             }
-            CU(vxrt_launch_denoise(odd ? h->d_pong : h->d_lighting, odd ? h->d_lighting : h->d_pong, h->d_depth, h->d_normal,
-                                   h->cfg.width, h->cfg.height, kDenoiseSizes[k], swap, r0, r1, h->stream, k > 0 && pdl,
-                                   k == 5 && fold ? &ff : nullptr));
+            if (e == cudaSuccess && brc == VXRT_OK) {
+                size_t n = 0;
+                e = cudaGraphGetNodes(graph, nullptr, &n);
+                std::vector<cudaGraphNode_t> nodes(n);
+                if (e == cudaSuccess) e = cudaGraphGetNodes(graph, nodes.data(), &n);
+                g.trace_node = nullptr;
+                for (size_t i = 0; e == cudaSuccess && i < n; i++) {
+                    cudaGraphNodeType t;
+                    if (cudaGraphNodeGetType(nodes[i], &t) != cudaSuccess || t != cudaGraphNodeTypeKernel) continue;
+                    cudaKernelNodeParams kp;
+                    if (cudaGraphKernelNodeGetParams(nodes[i], &kp) == cudaSuccess && kp.func == func) g.trace_node = nodes[i];
+                }
+                if (e == cudaSuccess && !g.trace_node) e = cudaErrorUnknown;
+                if (e == cudaSuccess) e = cudaGraphInstantiate(&g.exec, graph, 0);
+            }
+            if (e != cudaSuccess || brc != VXRT_OK) {                   // no graph on this handle: frames are issued launch by launch
+                cudaGetLastError();
+                if (g.exec) { cudaGraphExecDestroy(g.exec); g.exec = nullptr; }
+                if (graph) cudaGraphDestroy(graph);
+                h->graph_failed = true;
+            } else { g.graph = graph; g.func = func; g.grid = grid; g.block = block; }
+        } else {
+            cudaKernelNodeParams kp;
+            memset(&kp, 0, sizeof kp);
+            void* args[1] = {(void*)&P};
+            kp.func = (void*)func; kp.gridDim = grid; kp.blockDim = block; kp.sharedMemBytes = 0; kp.kernelParams = args;
+            CU(cudaGraphExecKernelNodeSetParams(g.exec, g.trace_node, &kp));
+        }
+        if (!h->graph_failed) {
+            CU(cudaGraphLaunch(g.exec, h->stream));
+            if (h->d_accum) accum_keeper(h)->frames_accumulated++;
+            h->rendered = true;
+            return VXRT_OK;
         }
     }
-    if (h->peer_on && (prc = vxrt_peer_after_denoise(h))) return prc;
-    CU(cudaEventRecord(h->ev[2], h->stream));
-    if (h->copy_pending[h->out_idx]) {
-        CU(cudaStreamWaitEvent(h->stream, h->ev_copy_done[h->out_idx], 0));
-        h->copy_pending[h->out_idx] = false;
-    }
-    if ((h->cfg.flags & VXRT_FLAG_FINALIZE) && !fold) {
-        VxrtPeerTail tail;
-        if (h->peer_on) tail = vxrt_peer_finalize_tail(h);
-        CU(vxrt_launch_finalize(h->d_albedo, h->d_emission, h->d_fog, h->d_lighting, h->d_depth, h->d_noise,
-                                h->peer_on ? vxrt_peer_output(h, h->out_idx) : h->d_output,       // peer mode: straight into the root's image
-                                h->cfg.width, h->cfg.height, h->row0, h->row1, h->stream, h->peer_on ? &tail : nullptr));
-    }
-    if (h->peer_on && (prc = vxrt_peer_end_frame(h))) return prc;
-    CU(cudaEventRecord(h->ev[3], h->stream));
+    if ((prc = issue_frame(h, P, f, false))) return prc;
+    if (h->d_accum) accum_keeper(h)->frames_accumulated++;
     h->rendered = true;
     return VXRT_OK;
 }

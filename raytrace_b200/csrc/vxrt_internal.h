@@ -117,6 +117,10 @@ struct VxrtHandle {
     void* peer_root_out[2] = {nullptr, nullptr};                 // the root's two output images
     std::vector<void*> peer_ipc_opened;
     cudaStream_t peer_stream = nullptr; cudaEvent_t ev_peer = nullptr;
+    // the frame as a CUDA graph, one per output image (api.cu): everything after the host-side waits, replayed with the trace
+    // node's parameters set per frame; re-captured when the trace kernel or its grid changes
+    struct FrameGraph { cudaGraph_t graph = nullptr; cudaGraphExec_t exec = nullptr; cudaGraphNode_t trace_node = nullptr; const void* func = nullptr; dim3 grid, block; };
+    FrameGraph graphs[2]; bool graph_failed = false;
 };
 void vxrt_comm_release(VxrtHandle* h);
 void vxrt_peer_release(VxrtHandle* h);
@@ -138,6 +142,9 @@ cudaError_t vxrt_preload_world(); cudaError_t vxrt_preload_peer(); cudaError_t v
 // launchers (each returns the cudaGetLastError() of its launch)
 cudaError_t vxrt_launch_trace(const TraceParams& p, cudaStream_t s);        // dispatches on p.fast
 cudaError_t vxrt_launch_trace_fast(const TraceParams& p, cudaStream_t s);
+// the kernel (and launch shape) vxrt_launch_trace runs for these parameters: the kernel node of a captured frame (api.cu)
+const void* vxrt_trace_kernel(const TraceParams& p, dim3* grid, dim3* block);
+const void* vxrt_trace_fast_kernel(const TraceParams& p, dim3* grid, dim3* block);
 // finalize.comp folded into the last denoise pass (post.cu k_denoise<.., FIN>): the images finalize reads besides lighting/depth
 struct VxrtFinalizeFold { const uchar4* albedo; const uchar4* emission; const uchar4* fog; const uint8_t* noise; uchar4* out; int row0, row1; };
 cudaError_t vxrt_launch_denoise(const ushort4* src, ushort4* dst, const uint16_t* depth, const uint8_t* normal,
