@@ -363,7 +363,7 @@ static int create_impl(const VxrtConfig* cfg, VxrtHandle* owner, VxrtHandle** ou
 
     auto init = [&]() -> int {
         // load every kernel now: a lazy load at first launch cannot complete while a peer-mode kernel spins on a flag
-        CU(vxrt_preload_trace()); CU(vxrt_preload_trace_fast()); CU(vxrt_preload_post()); CU(vxrt_preload_world()); CU(vxrt_preload_peer()); CU(vxrt_preload_temporal());
+        CU(vxrt_preload_trace()); CU(vxrt_preload_trace_fast()); CU(vxrt_preload_trace_pool()); CU(vxrt_preload_post()); CU(vxrt_preload_world()); CU(vxrt_preload_peer()); CU(vxrt_preload_temporal());
         CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
         for (int i = 0; i < 5; i++) CU(cudaEventCreate(&h->ev[i]));
         CU(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
@@ -422,6 +422,8 @@ static int create_impl(const VxrtConfig* cfg, VxrtHandle* owner, VxrtHandle** ou
             if ((rc = alloc_zero(h, (void**)&h->d_rays, P))) return rc;
             if ((rc = alloc_zero(h, (void**)&h->d_lighting_raw, P * 8))) return rc;
         }
+        if (cfg->mode == VXRT_MODE_FULL && !(cfg->flags & (VXRT_FLAG_HIT_BUFFERS | VXRT_FLAG_REPROJECT)) && cfg->width <= 4096 && cfg->height <= 4096)
+            if ((rc = alloc_zero(h, &h->d_pool_ctx, P * 16))) return rc;       // k_trace_pool's pixel records
         if (cfg->flags & VXRT_FLAG_ACCUMULATE) {
             if (owner) {                                                 // one running sum for the whole group of handles
                 if (!owner->d_accum || owner->cfg.width != cfg->width || owner->cfg.height != cfg->height || owner->row0 != h->row0 || owner->row1 != h->row1) {
@@ -490,7 +492,7 @@ void vxrt_destroy(VxrtHandle* h) {
     if (h->ev_world) cudaEventDestroy(h->ev_world);
     void* ptrs[] = {h->d_materials, h->d_minefield, h->d_noise, h->d_lut, h->d_dirty, h->d_edits, h->d_edit_table, h->d_lighting, h->d_pong,
                     h->d_lighting_raw, h->d_depth, h->d_normal, h->d_albedo, h->d_emission, h->d_fog, h->d_out_buf[0], h->d_out_buf[1],
-                    h->d_hit_voxel, h->d_hit_face, h->d_hit_word, h->d_hit_t, h->d_steps, h->d_rays, h->d_accum, h->d_counters,
+                    h->d_hit_voxel, h->d_hit_face, h->d_hit_word, h->d_hit_t, h->d_steps, h->d_rays, h->d_accum, h->d_counters, h->d_pool_ctx,
                     h->d_hit_pos[0], h->d_hit_pos[1], h->d_hist[0], h->d_hist[1], h->d_completed};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 2; i++) { if (h->h_edits[i]) cudaFreeHost(h->h_edits[i]); if (h->ev_edits[i]) cudaEventDestroy(h->ev_edits[i]); }
@@ -875,6 +877,7 @@ int vxrt_render_frame(VxrtHandle* h) {
     P.hit_voxel = h->d_hit_voxel; P.hit_face = h->d_hit_face; P.hit_word = h->d_hit_word; P.hit_t = h->d_hit_t;
     P.steps = h->d_steps; P.rays = h->d_rays;
     P.accum = h->d_accum;
+    P.pool_ctx = (h->cfg.flags & VXRT_FLAG_RAY_HANDOFF) ? nullptr : h->d_pool_ctx;
     if (h->d_hist[0]) h->hist_idx ^= 1;                                  // this frame's records; [hist_idx ^ 1] = the frame before
     P.hit_pos = h->d_hit_pos[h->hist_idx];
     P.counters = h->d_counters;
@@ -904,8 +907,9 @@ int vxrt_render_frame(VxrtHandle* h) {
         }
         VxrtHandle::FrameGraph& g = h->graphs[h->out_idx];
         dim3 grid, block;
-        const void* func = vxrt_trace_kernel(P, &grid, &block);
-        const bool same = g.exec && g.func == func && g.grid.x == grid.x && g.grid.y == grid.y && g.block.x == block.x;
+        size_t smem = 0;
+        const void* func = vxrt_trace_kernel(P, &grid, &block, &smem);
+        const bool same = g.exec && g.func == func && g.grid.x == grid.x && g.grid.y == grid.y && g.block.x == block.x && g.smem == smem;
         if (!same) {
             if (g.exec) { cudaGraphExecDestroy(g.exec); g.exec = nullptr; }
             if (g.graph) { cudaGraphDestroy(g.graph); g.graph = nullptr; }   // (kept while its exec lives: the node handle names a node of it)
@@ -936,12 +940,12 @@ int vxrt_render_frame(VxrtHandle* h) {
                 if (g.exec) { cudaGraphExecDestroy(g.exec); g.exec = nullptr; }
                 if (graph) cudaGraphDestroy(graph);
                 h->graph_failed = true;
-            } else { g.graph = graph; g.func = func; g.grid = grid; g.block = block; }
+            } else { g.graph = graph; g.func = func; g.grid = grid; g.block = block; g.smem = smem; }
         } else {
             cudaKernelNodeParams kp;
             memset(&kp, 0, sizeof kp);
             void* args[1] = {(void*)&P};
-            kp.func = (void*)func; kp.gridDim = grid; kp.blockDim = block; kp.sharedMemBytes = 0; kp.kernelParams = args;
+            kp.func = (void*)func; kp.gridDim = grid; kp.blockDim = block; kp.sharedMemBytes = (unsigned)smem; kp.kernelParams = args;
             CU(cudaGraphExecKernelNodeSetParams(g.exec, g.trace_node, &kp));
         }
         if (!h->graph_failed) {
@@ -1087,6 +1091,7 @@ int vxrt_frame_stats(VxrtHandle* h, VxrtFrameStats* out) {
     CU(cudaMemcpyAsync(c, h->d_counters, sizeof c, cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     { const int rc = peer_check(h); if (rc) return rc; }
+    if (c[6]) return fail(h, VXRT_ERR_STATE, "k_trace_pool: a ray ring overflowed (trace_pool.cu); the frame is void");
     out->rays = c[0]; out->steps = c[1]; out->hits = c[2]; out->noise_fetches = c[3]; out->limit_exhausted = c[4];
     CU(cudaEventElapsedTime(&out->trace_ms, h->ev[0], h->ev[1]));
     CU(cudaEventElapsedTime(&out->denoise_ms, h->ev[1], h->ev[2]));

@@ -207,8 +207,13 @@ __global__ void __launch_bounds__(128) k_trace_general(const __grid_constant__ T
 #define VXRT_PRELOAD(k) do { cudaFuncAttributes a_; cudaError_t e_ = cudaFuncGetAttributes(&a_, k); if (e_ != cudaSuccess) return e_; } while (0)
 cudaError_t vxrt_preload_trace() { VXRT_PRELOAD(k_trace_general); return cudaSuccess; }
 
-const void* vxrt_trace_kernel(const TraceParams& p, dim3* grid, dim3* block) {
-    if (p.fast) return vxrt_trace_fast_kernel(p, grid, block);
+const void* vxrt_trace_kernel(const TraceParams& p, dim3* grid, dim3* block, size_t* smem) {
+    *smem = 0;
+    if (p.fast) {
+        if (const void* k = vxrt_trace_pool_kernel(p, grid, block, smem)) return k;     // FULL lighting: rays pooled per warp (trace_pool.cu)
+        *smem = 0;
+        return vxrt_trace_fast_kernel(p, grid, block);
+    }
     *grid = dim3((p.width + 15) / 16, (p.row1 - p.row0 + 7) / 8);
     *block = dim3(128);
     return (const void*)k_trace_general;
@@ -217,7 +222,8 @@ const void* vxrt_trace_kernel(const TraceParams& p, dim3* grid, dim3* block) {
 cudaError_t vxrt_launch_trace(const TraceParams& p, cudaStream_t s) {
     if (p.row1 - p.row0 <= 0) return cudaSuccess;
     dim3 grid, block;
-    const void* k = vxrt_trace_kernel(p, &grid, &block);
+    size_t smem = 0;
+    const void* k = vxrt_trace_kernel(p, &grid, &block, &smem);
     void* args[1] = {(void*)&p};
-    return cudaLaunchKernel(k, grid, block, args, 0, s);
+    return cudaLaunchKernel(k, grid, block, args, smem, s);
 }

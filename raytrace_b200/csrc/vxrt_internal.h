@@ -50,6 +50,7 @@ struct TraceParams {
     // occupancy field as a 3-D texture over a block-linear cudaArray (layout A/B): 0 = linear array + LDG,
     // 1 = integer texel coordinates, 2 = normalised coordinates with wrap addressing (the unit does the floor and the mod)
     int field; unsigned long long field_tex; float inx, iny, inz;
+    void* pool_ctx;                      // 16 bytes per pixel for k_trace_pool (trace_pool.cu), or NULL
 };
 
 // temporal.cu: old_origin / old_transform_c0..2 of the frame block (pipeline.rs:213-227) and the images of the pass
@@ -102,6 +103,7 @@ struct VxrtHandle {
     uint16_t* d_depth; uint8_t* d_normal; uchar4 *d_albedo, *d_emission, *d_fog, *d_output;
     int32_t* d_hit_voxel; uint8_t* d_hit_face; uint32_t* d_hit_word; float* d_hit_t; uint32_t* d_steps; uint8_t* d_rays;
     float4* d_accum;
+    void* d_pool_ctx = nullptr;          // k_trace_pool's per-pixel records (FULL lighting without hit buffers)
     // temporal reprojection (temporal.cu): hit records and {mean light, count} of this frame and the one before
     float4* d_hit_pos[2] = {nullptr, nullptr}; float4* d_hist[2] = {nullptr, nullptr}; ushort4* d_completed = nullptr; int hist_idx = 0;
     unsigned long long* d_counters;
@@ -119,7 +121,7 @@ struct VxrtHandle {
     cudaStream_t peer_stream = nullptr; cudaEvent_t ev_peer = nullptr;
     // the frame as a CUDA graph, one per output image (api.cu): everything after the host-side waits, replayed with the trace
     // node's parameters set per frame; re-captured when the trace kernel or its grid changes
-    struct FrameGraph { cudaGraph_t graph = nullptr; cudaGraphExec_t exec = nullptr; cudaGraphNode_t trace_node = nullptr; const void* func = nullptr; dim3 grid, block; };
+    struct FrameGraph { cudaGraph_t graph = nullptr; cudaGraphExec_t exec = nullptr; cudaGraphNode_t trace_node = nullptr; const void* func = nullptr; dim3 grid, block; size_t smem = 0; };
     FrameGraph graphs[2]; bool graph_failed = false;
 };
 void vxrt_comm_release(VxrtHandle* h);
@@ -143,7 +145,9 @@ cudaError_t vxrt_preload_world(); cudaError_t vxrt_preload_peer(); cudaError_t v
 cudaError_t vxrt_launch_trace(const TraceParams& p, cudaStream_t s);        // dispatches on p.fast
 cudaError_t vxrt_launch_trace_fast(const TraceParams& p, cudaStream_t s);
 // the kernel (and launch shape) vxrt_launch_trace runs for these parameters: the kernel node of a captured frame (api.cu)
-const void* vxrt_trace_kernel(const TraceParams& p, dim3* grid, dim3* block);
+const void* vxrt_trace_kernel(const TraceParams& p, dim3* grid, dim3* block, size_t* smem);
+const void* vxrt_trace_pool_kernel(const TraceParams& p, dim3* grid, dim3* block, size_t* smem);   // trace_pool.cu; NULL = not applicable
+cudaError_t vxrt_preload_trace_pool();
 const void* vxrt_trace_fast_kernel(const TraceParams& p, dim3* grid, dim3* block);
 // finalize.comp folded into the last denoise pass (post.cu k_denoise<.., FIN>): the images finalize reads besides lighting/depth
 struct VxrtFinalizeFold { const uchar4* albedo; const uchar4* emission; const uchar4* fog; const uint8_t* noise; uchar4* out; int row0, row1; };

@@ -8,6 +8,11 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
+# k_trace_pool (trace_pool.cu) is opt-in and the library reads the switch once per process: the GPU suite runs with it on, so
+# every FULL-lighting handle WITHOUT hit buffers takes the pool and every handle with them the sequential form - both are compared
+os.environ.setdefault("VXRT_POOL", "1")
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
 

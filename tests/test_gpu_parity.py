@@ -1,6 +1,8 @@
 """GPU parity: libvxrt (through the C ABI) against the CPU oracle on the same seeded inputs.
 Integer outputs (hit voxel, face, material word, step and ray counts, G-buffer codes) are compared
 bit for bit; hit distance within 1e-4; colour within 1/255 (8-bit) or 1/255 of the 16-bit range."""
+import os
+
 import numpy as np
 import pytest
 
@@ -625,3 +627,39 @@ def test_duplicate_edits_last_entry_wins(orc, world):
             r.upload_world(m, f); r.apply_edits(e)
             gm, gf = r.read_world()
             assert np.array_equal(gm, want) and np.array_equal(gf, wf)
+
+
+@pytest.mark.parametrize("scene,width,height,lr", [("c1", 256, 256, (0, 0, 0)), ("mid", 320, 200, (0, 0, 0)), ("small", 72, 40, (0, 0, 0)),
+                                                   ("mid", 200, 120, (16, 0, -16))])
+def test_ray_pool_is_invisible(orc, world, noise, scene, width, height, lr):
+    """trace_pool.cu (VXRT_POOL=1): a FULL-lighting handle without hit buffers runs k_trace_pool (rays decoupled from lanes, refilled from a
+    per-warp queue).  Every ray and every fp32 operation of a pixel is that of the sequential form (k_trace_fast, which a handle
+    WITH hit buffers runs), so the images, the running sum and the frame counters are equal bit for bit, and both match the
+    oracle."""
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    dims = scenes.WORLDS[scene][0]
+    m, f = world(scene)
+    frames = []
+    assert os.environ.get("VXRT_POOL"), "run with VXRT_POOL=1 (tests/conftest.py sets it: the library reads it once per process)"
+    for k in range(3):
+        cam = scenes.camera(dims, k, 3)
+        o = tuple(c + l for c, l in zip(cam["origin"], lr))
+        frames.append(orc.fill_frame(o, cam["heading"], cam["pitch"], cam["sun_angle"], 40 + k, lr))
+    with R.Renderer(width, height, dims, N.MODE_FULL, N.FLAG_HIT_BUFFERS | N.FLAG_ACCUMULATE) as seq, \
+         R.Renderer(width, height, dims, N.MODE_FULL, N.FLAG_ACCUMULATE) as pool:
+        for r in (seq, pool):
+            r.upload_blue_noise(noise); r.upload_world(m, f)
+        fr = orc.Frame(width, height, accumulate=True)
+        for blk in frames:
+            ref = orc.render(m, f, noise, blk, N.MODE_FULL, width, height, frame=fr)
+            for r in (seq, pool):
+                r.set_frame(blk); r.render_frame()
+            a, b = seq.frame_stats(), pool.frame_stats()
+            assert (a.rays, a.steps, a.hits, a.noise_fetches, a.limit_exhausted) == (b.rays, b.steps, b.hits, b.noise_fetches, b.limit_exhausted)
+            assert (b.rays, b.steps, b.hits) == (ref.stats.rays, ref.stats.steps, ref.stats.hits)
+            for buf in (N.BUF_DEPTH, N.BUF_NORMAL, N.BUF_ALBEDO, N.BUF_EMISSION, N.BUF_FOG, N.BUF_LIGHTING, N.BUF_ACCUM):
+                assert np.array_equal(seq.read_buffer(buf), pool.read_buffer(buf)), buf
+            assert np.array_equal(pool.read_buffer(N.BUF_DEPTH), ref.depth) and np.array_equal(pool.read_buffer(N.BUF_NORMAL), ref.normal)
+            d = np.abs(pool.read_buffer(N.BUF_LIGHTING).astype(np.int64) - ref.lighting.astype(np.int64)).max()
+            assert d <= C16_TOL, d
