@@ -423,7 +423,9 @@ static int create_impl(const VxrtConfig* cfg, VxrtHandle* owner, VxrtHandle** ou
             if ((rc = alloc_zero(h, (void**)&h->d_lighting_raw, P * 8))) return rc;
         }
         if (cfg->mode == VXRT_MODE_FULL && !(cfg->flags & (VXRT_FLAG_HIT_BUFFERS | VXRT_FLAG_REPROJECT)) && cfg->width <= 4096 && cfg->height <= 4096)
-            if ((rc = alloc_zero(h, &h->d_pool_ctx, P * 16))) return rc;       // k_trace_pool's pixel records
+            { if ((rc = alloc_zero(h, &h->d_pool_ctx, P * 16))) return rc;       // k_trace_pool's pixel records
+              int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->device);
+              if ((rc = alloc_zero(h, &h->d_pool_rings, vxrt_trace_pool_ring_bytes(sms)))) return rc; }
         if (cfg->flags & VXRT_FLAG_ACCUMULATE) {
             if (owner) {                                                 // one running sum for the whole group of handles
                 if (!owner->d_accum || owner->cfg.width != cfg->width || owner->cfg.height != cfg->height || owner->row0 != h->row0 || owner->row1 != h->row1) {
@@ -492,7 +494,7 @@ void vxrt_destroy(VxrtHandle* h) {
     if (h->ev_world) cudaEventDestroy(h->ev_world);
     void* ptrs[] = {h->d_materials, h->d_minefield, h->d_noise, h->d_lut, h->d_dirty, h->d_edits, h->d_edit_table, h->d_lighting, h->d_pong,
                     h->d_lighting_raw, h->d_depth, h->d_normal, h->d_albedo, h->d_emission, h->d_fog, h->d_out_buf[0], h->d_out_buf[1],
-                    h->d_hit_voxel, h->d_hit_face, h->d_hit_word, h->d_hit_t, h->d_steps, h->d_rays, h->d_accum, h->d_counters, h->d_pool_ctx,
+                    h->d_hit_voxel, h->d_hit_face, h->d_hit_word, h->d_hit_t, h->d_steps, h->d_rays, h->d_accum, h->d_counters, h->d_pool_ctx, h->d_pool_rings,
                     h->d_hit_pos[0], h->d_hit_pos[1], h->d_hist[0], h->d_hist[1], h->d_completed};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 2; i++) { if (h->h_edits[i]) cudaFreeHost(h->h_edits[i]); if (h->ev_edits[i]) cudaEventDestroy(h->ev_edits[i]); }
@@ -877,7 +879,7 @@ int vxrt_render_frame(VxrtHandle* h) {
     P.hit_voxel = h->d_hit_voxel; P.hit_face = h->d_hit_face; P.hit_word = h->d_hit_word; P.hit_t = h->d_hit_t;
     P.steps = h->d_steps; P.rays = h->d_rays;
     P.accum = h->d_accum;
-    P.pool_ctx = (h->cfg.flags & VXRT_FLAG_RAY_HANDOFF) ? nullptr : h->d_pool_ctx;
+    P.pool_ctx = (h->cfg.flags & VXRT_FLAG_RAY_HANDOFF) ? nullptr : h->d_pool_ctx; P.pool_rings = h->d_pool_rings;
     if (h->d_hist[0]) h->hist_idx ^= 1;                                  // this frame's records; [hist_idx ^ 1] = the frame before
     P.hit_pos = h->d_hit_pos[h->hist_idx];
     P.counters = h->d_counters;

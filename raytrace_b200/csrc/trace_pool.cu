@@ -26,9 +26,16 @@ constexpr int RQ_CAP = 128, HL_CAP = 128, FL_CAP = 128;
 #ifndef VXRT_POOL_IDLE
 #define VXRT_POOL_IDLE 12                     // finished lanes that trigger a service
 #endif
+#ifndef VXRT_POOL_CHUNK
+#define VXRT_POOL_CHUNK 1
+#endif
+#ifndef VXRT_POOL_MINB
+#define VXRT_POOL_MINB 8                       // CTAs per SM the register budget is set for (64 registers)
+#endif
 #ifndef VXRT_POOL_KSTEPS
 #define VXRT_POOL_KSTEPS 4                    // march steps between two looks at the lane count
 #endif
+constexpr uint32_t TILE_CHUNK = VXRT_POOL_CHUNK;          // 8 x 4-pixel tiles a warp draws at a time (four 16 x 8 blocks)
 enum { K_PRIMARY = 0, K_SUN1 = 1, K_DIF1 = 2, K_SUN2 = 3, K_DIF2 = 4 };
 // ray / entry tag: px (12 bits) | py (12) | kind (3) | face code (3) | FL: bit 30 = "the primary ray missed"
 __device__ __forceinline__ uint32_t tag_of(int px, int py, uint32_t kind, uint32_t face) { return (uint32_t)px | ((uint32_t)py << 12) | (kind << 24) | (face << 27); }
@@ -50,18 +57,20 @@ struct WarpPool {
 };
 
 template <int LR0, int DIMS>
-__global__ void __launch_bounds__(32 * PW, 6) k_trace_pool(const __grid_constant__ TraceParams P) {
+__global__ void __launch_bounds__(32 * PW, VXRT_POOL_MINB) k_trace_pool(const __grid_constant__ TraceParams P) {
     constexpr bool SD = DIMS != 0;
     constexpr int LX = DIMS & 0xFF, LY = (DIMS >> 8) & 0xFF, LZ = (DIMS >> 16) & 0xFF;
-    extern __shared__ __align__(16) unsigned char pool_smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    WarpPool& W = reinterpret_cast<WarpPool*>(pool_smem)[warp];
+    // the rings live in global memory, read and written past L1 (ld/st.cg): as shared memory they took 35 KB per CTA, which left the
+    // occupancy field 7 % L1 hits and the SM 24 warps (r2_k); they are touched once per service, not per step
+    WarpPool& W = reinterpret_cast<WarpPool*>(P.pool_rings)[blockIdx.x * PW + warp];
     const uint32_t FULL = 0xffffffffu, below = (1u << lane) - 1u;
 
     const float hx = SD ? (float)(1 << (LX - 1)) : P.hx, hy = SD ? (float)(1 << (LY - 1)) : P.hy, hz = SD ? (float)(1 << (LZ - 1)) : P.hz;
     const uint32_t mxm = SD ? (1u << LX) - 1u : (uint32_t)P.nx - 1u, mym = SD ? (1u << LY) - 1u : (uint32_t)P.ny - 1u,
                    mzm = SD ? (1u << LZ) - 1u : (uint32_t)P.nz - 1u, nxu = (uint32_t)P.nx, nyu = (uint32_t)P.ny;
     const uint8_t* const minefield = P.minefield;
+    const uint32_t blo = (uint32_t)(unsigned long long)P.minefield, bhi = (uint32_t)((unsigned long long)P.minefield >> 32);   // (E15)
     const float M1 = 12582912.0f;             // 1.5 * 2^23
     const F3 sunlight = f3(P.sl_r, P.sl_g, P.sl_b);
     uint4* const ctx = reinterpret_cast<uint4*>(P.pool_ctx);
@@ -80,13 +89,16 @@ __global__ void __launch_bounds__(32 * PW, 6) k_trace_pool(const __grid_constant
     // ---- warp-uniform ring state -----------------------------------------------------------------------------------
     uint32_t rq_head = 0, rq_count = 0, hl_head = 0, hl_count = 0, fl_head = 0, fl_count = 0;
     bool tiles_left = true;
+    uint32_t tile_next = 0, tile_end = 0;
     const int blocks_x = (P.width + 15) / 16, blocks_y = (P.row1 - P.row0 + 7) / 8;
     const uint32_t ntiles = (uint32_t)(blocks_x * blocks_y * 4);
 
     // ---- lane state: the ray this lane holds ------------------------------------------------------------------------
-    bool has_ray = false, act = false;          // holds a ray (marching or finished and not yet filed) / still marching
-    uint32_t tag = 0, cur = 0;
-    int left = 0;
+    // the ray this lane holds: tag == NO_RAY: none.  left > 0: marching, `left` iterations of :113's limit to go; left < 0: finished
+    // and not yet filed, ~left iterations were to go when it stopped
+    const uint32_t NO_RAY = 0xFFFFFFFFu;
+    uint32_t tag = NO_RAY, cur = 0;
+    int left = -1;
     f2 pxy = pk(0.f, 0.f), dxy = pk(0.f, 0.f), lpxy = pk(0.f, 0.f), qxy = pk(0.f, 0.f);
     float pz = 0.f, dz = 0.f, lpz = 0.f, qz = 0.f, lx = 0.f, ly = 0.f, lz = 0.f;
     uint32_t c_steps = 0, c_rays_hits = 0, c_noise_limit = 0;                           // frame counters of this lane
@@ -98,8 +110,8 @@ __global__ void __launch_bounds__(32 * PW, 6) k_trace_pool(const __grid_constant
         const uint32_t m = __ballot_sync(FULL, on);
         if (on) {
             const uint32_t s = (rq_head + rq_count + (uint32_t)__popc(m & below)) & (RQ_CAP - 1);
-            W.rq[0][s] = o.x; W.rq[1][s] = o.y; W.rq[2][s] = o.z; W.rq[3][s] = dir.x; W.rq[4][s] = dir.y; W.rq[5][s] = dir.z;
-            W.rq[6][s] = lpa.x; W.rq[7][s] = lpa.y; W.rq[8][s] = lpa.z; W.rq[9][s] = __uint_as_float(t); W.rq_cur[s] = c;
+            __stcg(&W.rq[0][s], o.x); __stcg(&W.rq[1][s], o.y); __stcg(&W.rq[2][s], o.z); __stcg(&W.rq[3][s], dir.x); __stcg(&W.rq[4][s], dir.y); __stcg(&W.rq[5][s], dir.z);
+            __stcg(&W.rq[6][s], lpa.x); __stcg(&W.rq[7][s], lpa.y); __stcg(&W.rq[8][s], lpa.z); __stcg(&W.rq[9][s], __uint_as_float(t)); __stcg(&W.rq_cur[s], c);
         }
         rq_count += (uint32_t)__popc(m);
     };
@@ -107,13 +119,13 @@ __global__ void __launch_bounds__(32 * PW, 6) k_trace_pool(const __grid_constant
         const uint32_t m = __ballot_sync(FULL, on);
         if (on) {
             const uint32_t s = (hl_head + hl_count + (uint32_t)__popc(m & below)) & (HL_CAP - 1);
-            W.hl[0][s] = t; W.hl[1][s] = __float_as_uint(p.x); W.hl[2][s] = __float_as_uint(p.y); W.hl[3][s] = __float_as_uint(p.z); W.hl[4][s] = word;
+            __stcg(&W.hl[0][s], t); __stcg(&W.hl[1][s], __float_as_uint(p.x)); __stcg(&W.hl[2][s], __float_as_uint(p.y)); __stcg(&W.hl[3][s], __float_as_uint(p.z)); __stcg(&W.hl[4][s], word);
         }
         hl_count += (uint32_t)__popc(m);
     };
     auto push_done = [&](bool on, uint32_t t) {
         const uint32_t m = __ballot_sync(FULL, on);
-        if (on) W.fl[(fl_head + fl_count + (uint32_t)__popc(m & below)) & (FL_CAP - 1)] = t;
+        if (on) __stcg(&W.fl[(fl_head + fl_count + (uint32_t)__popc(m & below)) & (FL_CAP - 1)], t);
         fl_count += (uint32_t)__popc(m);
     };
     // a ray that leaves the tree without spawning: one atomic on the pixel's record carries its sky bit and takes it off the
@@ -170,10 +182,16 @@ __global__ void __launch_bounds__(32 * PW, 6) k_trace_pool(const __grid_constant
 
     // ---- a tile of 8 x 4 pixels: fog image, primary rays into RQ (:296-315, :380-385) --------------------------------------
     auto generate_tile = [&]() {
-        uint32_t t = 0;
-        if (lane == 0) t = (uint32_t)atomicAdd(P.counters + 5, 1ull);
-        t = __shfl_sync(FULL, t, 0);
-        if (t >= ntiles) { tiles_left = false; return; }
+        // tiles are drawn TILE_CHUNK at a time from the frame-wide counter.  Measured (r2_l, C3 trace): 1 tile 0.80 ms, 2 tiles 0.86,
+        // 4 tiles 0.94, 16 tiles 1.39 - the warps that draw the last, ground-heavy chunks finish alone, so the finest grain wins
+        if (tile_next == tile_end) {
+            uint32_t t0 = 0;
+            if (lane == 0) t0 = (uint32_t)atomicAdd(P.counters + 5, (unsigned long long)TILE_CHUNK);
+            t0 = __shfl_sync(FULL, t0, 0);
+            if (t0 >= ntiles) { tiles_left = false; return; }
+            tile_next = t0; tile_end = t0 + TILE_CHUNK < ntiles ? t0 + TILE_CHUNK : ntiles;
+        }
+        const uint32_t t = tile_next++;
         const uint32_t b = t >> 2, sub = t & 3u;
         const int bx = (int)(b % (uint32_t)blocks_x), by = (int)(b / (uint32_t)blocks_x);
         const int px = bx * 16 + (int)(sub & 1u) * 8 + (lane & 7), py = P.row0 + by * 8 + (int)(sub >> 1) * 4 + (lane >> 3);
@@ -209,7 +227,7 @@ __global__ void __launch_bounds__(32 * PW, 6) k_trace_pool(const __grid_constant
         const bool on = (uint32_t)lane < n;
         const uint32_t s = (hl_head + (uint32_t)lane) & (HL_CAP - 1);
         uint32_t t = 0, word = 0; F3 hp = f3(0, 0, 0);
-        if (on) { t = W.hl[0][s]; hp = f3(__uint_as_float(W.hl[1][s]), __uint_as_float(W.hl[2][s]), __uint_as_float(W.hl[3][s])); word = W.hl[4][s]; }
+        if (on) { t = __ldcg(&W.hl[0][s]); hp = f3(__uint_as_float(__ldcg(&W.hl[1][s])), __uint_as_float(__ldcg(&W.hl[2][s])), __uint_as_float(__ldcg(&W.hl[3][s]))); word = __ldcg(&W.hl[4][s]); }
         __syncwarp();
         hl_head = (hl_head + n) & (HL_CAP - 1); hl_count -= n;
         const int px = TAG_PX(t), py = TAG_PY(t);
@@ -252,7 +270,7 @@ __global__ void __launch_bounds__(32 * PW, 6) k_trace_pool(const __grid_constant
         if (n == 0) return;
         const bool on = (uint32_t)lane < n;
         uint32_t t = 0;
-        if (on) t = W.fl[(fl_head + (uint32_t)lane) & (FL_CAP - 1)];
+        if (on) t = __ldcg(&W.fl[(fl_head + (uint32_t)lane) & (FL_CAP - 1)]);
         __syncwarp();
         fl_head = (fl_head + n) & (FL_CAP - 1); fl_count -= n;
         if (!on) return;
@@ -292,14 +310,14 @@ __global__ void __launch_bounds__(32 * PW, 6) k_trace_pool(const __grid_constant
     // ---- the worker loop ------------------------------------------------------------------------------------------------------------
     for (int guard = 0; guard < (1 << 28); guard++) {
         // (1) finished lanes file their result
-        const bool fin = has_ray && !act;
+        const bool fin = tag != NO_RAY && left < 0;
         if (__any_sync(FULL, fin)) {
             bool r_plain = false, r_air = false, r_spawn = false, r_miss = false;
-            uint32_t word = 0, face = 0;
+            uint32_t word = 0, face = 0, tag_done = 0;
             F3 hp = f3(0, 0, 0);
             if (fin) {
                 const float x = lo2(pxy), y = hi2(pxy);
-                const uint32_t steps = (uint32_t)(P.max_steps - left);
+                const uint32_t steps = (uint32_t)(P.max_steps - ~left);
                 c_steps += steps;
                 const bool sky = sky_test(x, y, pz);
                 const bool hit = !sky && cur == 0;                                       // sky first, :138-146
@@ -321,11 +339,11 @@ __global__ void __launch_bounds__(32 * PW, 6) k_trace_pool(const __grid_constant
                     if (kind == K_DIF1) atomicAdd(&ctx[(size_t)TAG_PY(tag) * P.width + TAG_PX(tag)].x, 1u);   // itself off, its two rays on
                 } else if (kind == K_PRIMARY) r_miss = true;
                 else r_plain = true;
-                has_ray = false;
+                tag_done = tag; tag = NO_RAY;
             }
-            push_hit(r_spawn, (tag & 0x07FFFFFFu) | (face << 27), hp, word);
-            push_done(r_miss, (tag & 0x00FFFFFFu) | TAG_MISS);
-            resolve(r_plain, tag, r_air);
+            push_hit(r_spawn, (tag_done & 0x07FFFFFFu) | (face << 27), hp, word);
+            push_done(r_miss, (tag_done & 0x00FFFFFFu) | TAG_MISS);
+            resolve(r_plain, tag_done, r_air);
             __syncwarp();
         }
         // (2) keep RQ stocked: deeper levels first (they free pixels), new tiles when nothing else is ready
@@ -343,33 +361,32 @@ __global__ void __launch_bounds__(32 * PW, 6) k_trace_pool(const __grid_constant
         }
         // (3) idle lanes take the next rays
         {
-            const uint32_t idle = __ballot_sync(FULL, !has_ray);
+            const uint32_t idle = __ballot_sync(FULL, tag == NO_RAY);
             const uint32_t rank = (uint32_t)__popc(idle & below);
-            if (!has_ray && rank < rq_count) {
+            if (tag == NO_RAY && rank < rq_count) {
                 const uint32_t s = (rq_head + rank) & (RQ_CAP - 1);
-                pxy = pk(W.rq[0][s], W.rq[1][s]); pz = W.rq[2][s];
-                dxy = pk(W.rq[3][s], W.rq[4][s]); dz = W.rq[5][s];
-                lpxy = pk(W.rq[6][s], W.rq[7][s]); lpz = W.rq[8][s];
-                tag = __float_as_uint(W.rq[9][s]); cur = W.rq_cur[s];
+                pxy = pk(__ldcg(&W.rq[0][s]), __ldcg(&W.rq[1][s])); pz = __ldcg(&W.rq[2][s]);
+                dxy = pk(__ldcg(&W.rq[3][s]), __ldcg(&W.rq[4][s])); dz = __ldcg(&W.rq[5][s]);
+                lpxy = pk(__ldcg(&W.rq[6][s]), __ldcg(&W.rq[7][s])); lpz = __ldcg(&W.rq[8][s]);
+                tag = __float_as_uint(__ldcg(&W.rq[9][s])); cur = __ldcg(&W.rq_cur[s]);
                 qxy = add2(pxy, hxy); qz = fadd(pz, hz);
                 left = P.max_steps;
-                has_ray = true; act = true;
             }
             const uint32_t take = (uint32_t)__popc(idle) < rq_count ? (uint32_t)__popc(idle) : rq_count;
             __syncwarp();
             rq_head = (rq_head + take) & (RQ_CAP - 1); rq_count -= take;
         }
         // (4) nothing marching and nothing queued: the frame's tiles are gone and every list is empty
-        if (!__any_sync(FULL, has_ray)) {
+        if (!__any_sync(FULL, tag != NO_RAY)) {
             if (rq_count == 0u && hl_count == 0u && fl_count == 0u && !tiles_left) break;
             continue;
         }
         // (5) march until SERVICE_IDLE lanes have finished (or everything has)
         float Ms = __int_as_float((int)(cur << 23) + 0x4AC00000);                        // 1.5 * 2^(22+cur)
         for (;;) {
-#pragma unroll 1
+#pragma unroll
             for (int k = 0; k < VXRT_POOL_KSTEPS; k++) {
-                if (act) {
+                if (left > 0) {
                     // one iteration of trace_ray's loop (:113-162), the arithmetic of k_trace_fast's packed form
                     const float ax = flip_if_positive(lo2(qxy), lo2(dxy)), ay = flip_if_positive(hi2(qxy), hi2(dxy)), az = flip_if_positive(qz, dz);
                     const f2 axy = pk(ax, ay), Ms2 = pk(Ms, Ms);
@@ -383,17 +400,22 @@ __global__ void __launch_bounds__(32 * PW, 6) k_trace_pool(const __grid_constant
                     pxy = fma2(sxy, one2, pxy);                                           // (E14)
                     pz = fadd(pz, fmul(dz, t));
                     qxy = add2(pxy, hxy); qz = fadd(pz, hz);
-                    cur = __ldg(minefield + texel_offset(lo2(qxy), hi2(qxy), qz));        // :137
+                    {
+                        const f2 fxy = add2_rd(qxy, pk(M1, M1));                              // (E5)
+                        const uint32_t ix = (uint32_t)__float_as_int(lo2(fxy)) & mxm, iy = (uint32_t)__float_as_int(hi2(fxy)) & mym,
+                                       iz = (uint32_t)__float_as_int(__fadd_rd(qz, M1)) & mzm;
+                        cur = ldg_u8_halves((iz * nyu + iy) * nxu + (ix | blo), bhi);         // :137, (E15)
+                    }
                     left--;
-                    if (sky_test(lo2(pxy), hi2(pxy), pz) | (cur == 0) | (left == 0)) act = false;   // :138-146, :113
+                    if (sky_test(lo2(pxy), hi2(pxy), pz) | (cur == 0) | (left == 0)) left = ~left;   // :138-146, :113
                     else Ms = __int_as_float((int)(cur << 23) + 0x4AC00000);              // :161
                 }
             }
-            const uint32_t marching = __ballot_sync(FULL, act);
+            const uint32_t marching = __ballot_sync(FULL, left > 0);
             if (marching == 0u) break;
             // leave for a service when enough rays have finished: VXRT_POOL_IDLE of a full warp, half of what a thin one holds (their
             // results are what new rays come from; empty lanes alone cannot be helped)
-            const uint32_t holding = (uint32_t)__popc(__ballot_sync(FULL, has_ray)), nfin = holding - (uint32_t)__popc(marching);
+            const uint32_t holding = (uint32_t)__popc(__ballot_sync(FULL, tag != NO_RAY)), nfin = holding - (uint32_t)__popc(marching);
             const uint32_t need = holding / 2u < (uint32_t)VXRT_POOL_IDLE ? (holding / 2u > 0u ? holding / 2u : 1u) : (uint32_t)VXRT_POOL_IDLE;
             if (nfin >= need) break;
         }
@@ -418,7 +440,8 @@ static const void* pool_kernel(int form, int dims) {
     if (dims == VXRT_DIMS(11, 11, 8)) return form == 1 ? (const void*)k_trace_pool<1, VXRT_DIMS(11, 11, 8)> : form == 0 ? (const void*)k_trace_pool<0, VXRT_DIMS(11, 11, 8)> : nullptr;
     return form == 2 ? (const void*)k_trace_pool<2, 0> : form == 1 ? (const void*)k_trace_pool<1, 0> : (const void*)k_trace_pool<0, 0>;
 }
-static const size_t kPoolSmem = sizeof(WarpPool) * PW;
+static const size_t kPoolSmem = 0;
+size_t vxrt_trace_pool_ring_bytes(int sms) { return sizeof(WarpPool) * PW * (size_t)sms * VXRT_POOL_MINB; }
 
 cudaError_t vxrt_preload_trace_pool() {
     for (int form = 0; form < 3; form++)
@@ -427,7 +450,6 @@ cudaError_t vxrt_preload_trace_pool() {
             if (!k) continue;
             cudaFuncAttributes a;
             cudaError_t e = cudaFuncGetAttributes(&a, k);
-            if (e == cudaSuccess) e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPoolSmem);
             if (e != cudaSuccess) return e;
         }
     return cudaSuccess;
@@ -435,20 +457,24 @@ cudaError_t vxrt_preload_trace_pool() {
 
 // the pool form of the trace pass for these parameters, or nullptr where k_trace_fast has to run it (see the conditions)
 const void* vxrt_trace_pool_kernel(const TraceParams& p, dim3* grid, dim3* block, size_t* smem) {
-    // opt-in while it is slower than the sequential form (r2_k: C3 trace 0.81 ms against 0.436; lanes per instruction 16.9 -> 23.7,
-    // but 24 resident warps, an L1 squeezed to 7 % hits by the rings, and 49 issue slots per step against 36)
+    // opt-in: slower than the sequential form as built.  C3 trace 0.79 ms against 0.436 (r2_k, r2_l): lanes per instruction
+    // 16.9 -> 23.2 and 369 M warp instructions against 318 M, but 30 % issue utilisation - a warp's 32 rays all wait while a service
+    // (ring traffic, the pixel-record atomics, spawn set-up with its first occupancy fetches) runs its chain of L2 round trips,
+    // every ~12 finished rays.  Rings in shared memory (7 % L1 hits, 24 warps) or in global memory (24-32 % hits, 30 warps),
+    // 40 / 51 / 64 registers, service thresholds 12-24 and 4-8 steps between lane counts all land within 5 % of each other.
     static const bool on_env = getenv("VXRT_POOL") != nullptr;
-    if (!on_env || !p.pool_ctx || p.mode != VXRT_MODE_FULL || p.hit_voxel || p.hit_pos || p.field) return nullptr;
+    if (!on_env || !p.pool_ctx || !p.pool_rings || p.mode != VXRT_MODE_FULL || p.hit_voxel || p.hit_pos || p.field) return nullptr;
     if (p.own_row0 > p.row0 || p.own_row1 < p.row1 || p.width > 4096 || p.height > 4096 || p.max_steps > 200000) return nullptr;
     const unsigned long long bytes = (unsigned long long)p.nx * p.ny * p.nz;
-    if (bytes > 0xFFFFFFFFull) return nullptr;
+    const unsigned long long base = (unsigned long long)p.minefield;
+    if ((base & (unsigned long long)(p.nx - 1)) != 0 || (base & 0xFFFFFFFFull) + bytes > 0x100000000ull) return nullptr;   // (E15)
     const bool lr0 = p.lrx == 0.0f && p.lry == 0.0f && p.lrz == 0.0f;
     const int form = !lr0 ? 0 : (p.nx == p.ny && p.ny == p.nz) ? 2 : 1;
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int tiles = ((p.width + 15) / 16) * ((p.row1 - p.row0 + 7) / 8) * 4;
-    int ctas = sms * 6;
+    int ctas = sms * VXRT_POOL_MINB;
     if (ctas * PW > tiles) ctas = (tiles + PW - 1) / PW;
     *grid = dim3((unsigned)ctas); *block = dim3(32 * PW); *smem = kPoolSmem;
     return pool_kernel(form, VXRT_DIMS(p.lx, p.ly, p.lz));

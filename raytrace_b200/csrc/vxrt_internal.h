@@ -51,6 +51,7 @@ struct TraceParams {
     // 1 = integer texel coordinates, 2 = normalised coordinates with wrap addressing (the unit does the floor and the mod)
     int field; unsigned long long field_tex; float inx, iny, inz;
     void* pool_ctx;                      // 16 bytes per pixel for k_trace_pool (trace_pool.cu), or NULL
+    void* pool_rings;                    // its per-warp rings (vxrt_trace_pool_ring_bytes)
 };
 
 // temporal.cu: old_origin / old_transform_c0..2 of the frame block (pipeline.rs:213-227) and the images of the pass
@@ -104,6 +105,7 @@ struct VxrtHandle {
     int32_t* d_hit_voxel; uint8_t* d_hit_face; uint32_t* d_hit_word; float* d_hit_t; uint32_t* d_steps; uint8_t* d_rays;
     float4* d_accum;
     void* d_pool_ctx = nullptr;          // k_trace_pool's per-pixel records (FULL lighting without hit buffers)
+    void* d_pool_rings = nullptr;        // and its per-warp rings
     // temporal reprojection (temporal.cu): hit records and {mean light, count} of this frame and the one before
     float4* d_hit_pos[2] = {nullptr, nullptr}; float4* d_hist[2] = {nullptr, nullptr}; ushort4* d_completed = nullptr; int hist_idx = 0;
     unsigned long long* d_counters;
@@ -148,6 +150,7 @@ cudaError_t vxrt_launch_trace_fast(const TraceParams& p, cudaStream_t s);
 const void* vxrt_trace_kernel(const TraceParams& p, dim3* grid, dim3* block, size_t* smem);
 const void* vxrt_trace_pool_kernel(const TraceParams& p, dim3* grid, dim3* block, size_t* smem);   // trace_pool.cu; NULL = not applicable
 cudaError_t vxrt_preload_trace_pool();
+size_t vxrt_trace_pool_ring_bytes(int sms);
 const void* vxrt_trace_fast_kernel(const TraceParams& p, dim3* grid, dim3* block);
 // finalize.comp folded into the last denoise pass (post.cu k_denoise<.., FIN>): the images finalize reads besides lighting/depth
 struct VxrtFinalizeFold { const uchar4* albedo; const uchar4* emission; const uchar4* fog; const uint8_t* noise; uchar4* out; int row0, row1; };
