@@ -178,6 +178,20 @@ int  vxrt_apply_edits(VxrtHandle* h, const VxrtEdit* edits, size_t n);
 /* Same with the edit list already on the device (e.g. after an NCCL broadcast). */
 int  vxrt_apply_edits_device(VxrtHandle* h, const void* d_edits, size_t n);
 
+/* No counterpart in the reference.  The edit path for callers that may not allocate
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): scatters the n edits of a DEVICE list into
+ * the caller's own window arrays (d_materials u32 / d_minefield u8, [nz][ny][nx], x fastest) with vxrt_apply_edits' last-entry-wins
+ * rule and rebuilds the occupancy field of every touched 64^3 chunk (pack_into rule), asynchronously on `cuda_stream` (a
+ * cudaStream_t; NULL = the default stream).  It calls no cudaMalloc / cudaFree: its scratch (last-wins table + per-chunk dirty
+ * flags, 896 KiB) is one file-scope device array that every GPU that loads the library holds until exit.  Limits: n <=
+ * VXRT_STATIC_MAX_EDITS, window chunks (nx/64 * ny/64 * nz/64) <= VXRT_STATIC_MAX_CHUNKS; beyond them VXRT_ERR_SIZE (text from
+ * vxrt_last_error(NULL)).  Every call on a device shares the array, which is cleared at the start of each call: calls that overlap
+ * on the GPU (different streams without ordering) race. */
+#define VXRT_STATIC_MAX_EDITS  16384
+#define VXRT_STATIC_MAX_CHUNKS 32768
+int  vxrt_apply_edits_static(int device, uint32_t* d_materials, uint8_t* d_minefield, int nx, int ny, int nz,
+                             const VxrtEdit* d_edits, size_t n, void* cuda_stream);
+
 /* ---- per frame ---------------------------------------------------------------------- */
 /* replaces the uniform fill + mapped-buffer memcpy of draw_frame (pipeline.rs:195-211) */
 int  vxrt_set_frame(VxrtHandle* h, const VxrtFrameParams* p);

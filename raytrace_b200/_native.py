@@ -79,6 +79,7 @@ SYMBOLS = {
     "vxrt_upload_blue_noise": (C.c_int, [_H, C.c_void_p, C.c_size_t]),
     "vxrt_apply_edits": (C.c_int, [_H, C.c_void_p, C.c_size_t]),
     "vxrt_apply_edits_device": (C.c_int, [_H, C.c_void_p, C.c_size_t]),
+    "vxrt_apply_edits_static": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),
     "vxrt_set_frame": (C.c_int, [_H, C.c_void_p]),
     "vxrt_render_frame": (C.c_int, [_H]),
     "vxrt_sync": (C.c_int, [_H]),
@@ -112,6 +113,7 @@ SYMBOLS = {
     "vxrt_peer_attach": (C.c_int, [_H, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_int]),
     "vxrt_selftest_division": (C.c_int, [C.c_int, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64)]),
 }
+STATIC_MAX_EDITS, STATIC_MAX_CHUNKS = 16384, 32768
 COMM_ID_BYTES = 128
 PEER_BLOB_BYTES = 512
 

@@ -242,6 +242,8 @@ int rebuild_dirty(VxrtHandle* h) {
 
 }  // namespace
 
+void vxrt_set_global_error(const char* msg) { g_create_error = msg ? msg : ""; }
+
 extern "C" {
 
 int vxrt_abi_version(void) { return VXRT_ABI_VERSION; }

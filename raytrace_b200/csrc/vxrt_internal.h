@@ -126,6 +126,8 @@ struct VxrtHandle {
     struct FrameGraph { cudaGraph_t graph = nullptr; cudaGraphExec_t exec = nullptr; cudaGraphNode_t trace_node = nullptr; const void* func = nullptr; dim3 grid, block; size_t smem = 0; };
     FrameGraph graphs[2]; bool graph_failed = false;
 };
+// error text of calls that have no handle (read back with vxrt_last_error(NULL))
+void vxrt_set_global_error(const char* msg);
 void vxrt_comm_release(VxrtHandle* h);
 void vxrt_peer_release(VxrtHandle* h);
 int vxrt_peer_begin_frame(VxrtHandle* h, int out_idx);

@@ -5,6 +5,7 @@
 //   k_generate_*       replaces src/world/generate.rs for SYNTHETIC, SEEDED inputs (the reference
 //                      generator draws from thread_rng and is not reproducible)
 #include "vxrt_internal.h"
+#include <mutex>
 
 namespace {
 
@@ -281,4 +282,68 @@ cudaError_t vxrt_launch_generate(uint32_t* materials, int nx, int ny, int nz, in
     dim3 grid((nx + 31) / 32, (ny + 7) / 8);
     k_generate<<<grid, 256, 0, s>>>(materials, G);
     return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// vxrt_apply_edits_static: the edit path (k_claim_edits + k_apply_edits + k_build_minefield of the touched chunks) for callers
+// that may not allocate - code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc.  No counterpart
+// in the reference.  The scratch vxrt_apply_edits keeps per handle in cudaMalloc'd
+// memory (the last-wins table and the per-chunk dirty flags) lives here in ONE file-scope device array of fixed size, which every
+// GPU that loads the library holds until exit (896 KiB).  Every call shares it: it is cleared on the caller's stream at the start
+// of each call, and two calls that overlap on the GPU race on it.
+// ---------------------------------------------------------------------------------------------
+constexpr size_t kStaticEditSlots = (size_t)4 * VXRT_STATIC_MAX_EDITS;            // table slots: 4 per edit (load factor <= 1/4)
+constexpr size_t kStaticScratchBytes = kStaticEditSlots * 12 + (size_t)VXRT_STATIC_MAX_CHUNKS * 4;
+static __device__ __align__(256) unsigned char g_static_edit_scratch[kStaticScratchBytes];   // keys (8 B) | winners (4 B) | dirty flags (4 B)
+
+// The array's name is a host-side stand-in in host code, not a device address: the address is asked for once per device, with
+// that device current, and cached.
+static int static_scratch_address(int device, unsigned char** out, std::string* err) {
+    static std::mutex mu;
+    static unsigned char* cached[64] = {nullptr};
+    if (device < 0 || device >= 64) { *err = "vxrt_apply_edits_static: device ordinal out of range"; return VXRT_ERR_INVALID; }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!cached[device]) {
+        cudaError_t e = cudaSetDevice(device);
+        void* ptr = nullptr;
+        if (e == cudaSuccess) e = cudaGetSymbolAddress(&ptr, g_static_edit_scratch);
+        if (e != cudaSuccess || !ptr) { *err = std::string("vxrt_apply_edits_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e); return VXRT_ERR_CUDA; }
+        cached[device] = (unsigned char*)ptr;
+    }
+    *out = cached[device];
+    return VXRT_OK;
+}
+
+extern "C" int vxrt_apply_edits_static(int device, uint32_t* d_materials, uint8_t* d_minefield, int nx, int ny, int nz,
+                                       const VxrtEdit* d_edits, size_t n, void* cuda_stream) {
+    std::string err;
+    auto fail = [&](int code, const std::string& msg) { vxrt_set_global_error(msg.c_str()); return code; };
+    auto pow2 = [](int v) { return v >= 64 && v <= 4096 && (v & (v - 1)) == 0; };
+    if (!d_materials || !d_minefield || (n && !d_edits)) return fail(VXRT_ERR_INVALID, "vxrt_apply_edits_static: NULL device pointer");
+    if (!pow2(nx) || !pow2(ny) || !pow2(nz)) return fail(VXRT_ERR_INVALID, "vxrt_apply_edits_static: window dims must be powers of two in [64, 4096]");
+    const size_t chunks = (size_t)(nx >> 6) * (ny >> 6) * (nz >> 6);
+    if (n > (size_t)VXRT_STATIC_MAX_EDITS)
+        return fail(VXRT_ERR_SIZE, "vxrt_apply_edits_static: more than VXRT_STATIC_MAX_EDITS (16384) edits in one call; split the list or use vxrt_apply_edits");
+    if (chunks > (size_t)VXRT_STATIC_MAX_CHUNKS)
+        return fail(VXRT_ERR_SIZE, "vxrt_apply_edits_static: window has more than VXRT_STATIC_MAX_CHUNKS (32768) chunks; use vxrt_apply_edits");
+    if (n == 0) return VXRT_OK;
+    unsigned char* scratch = nullptr;
+    const int rc = static_scratch_address(device, &scratch, &err);
+    if (rc != VXRT_OK) return fail(rc, err);
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return fail(VXRT_ERR_CUDA, std::string("vxrt_apply_edits_static: cudaSetDevice: ") + cudaGetErrorString(e));
+    cudaStream_t s = (cudaStream_t)cuda_stream;
+    unsigned long long* keys = (unsigned long long*)scratch;
+    uint32_t* winner = (uint32_t*)(scratch + kStaticEditSlots * 8);
+    uint32_t* dirty = (uint32_t*)(scratch + kStaticEditSlots * 12);
+    // the array keeps the last call's contents: table and flags start at zero
+    e = cudaMemsetAsync(scratch, 0, kStaticEditSlots * 12 + chunks * 4, s);
+    if (e != cudaSuccess) return fail(VXRT_ERR_CUDA, std::string("vxrt_apply_edits_static: cudaMemsetAsync: ") + cudaGetErrorString(e));
+    const unsigned blocks = (unsigned)((n + 255) / 256);
+    k_claim_edits<<<blocks, 256, 0, s>>>(d_edits, n, nx, ny, nz, keys, winner, (uint32_t)(kStaticEditSlots - 1));
+    k_apply_edits<<<blocks, 256, 0, s>>>(d_materials, dirty, d_edits, n, nx, ny, nz, keys, winner, (uint32_t)(kStaticEditSlots - 1));
+    k_build_minefield<<<(unsigned)chunks, 512, 0, s>>>(d_materials, d_minefield, nx, ny, nz, dirty);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(VXRT_ERR_CUDA, std::string("vxrt_apply_edits_static: launch: ") + cudaGetErrorString(e));
+    return VXRT_OK;
 }
