@@ -234,6 +234,15 @@ int  vxrt_frame_stats(VxrtHandle* h, VxrtFrameStats* out);  /* syncs the stream 
 /* Kernels one vxrt_render_frame launches on this handle outside peer mode: the trace pass, the six denoise passes, k_finalize
  * (VXRT_FOLD=1 in the environment folds it into the last denoise launch), k_reproject with VXRT_FLAG_REPROJECT. */
 int  vxrt_launches_per_frame(const VxrtHandle* h);
+/* Form of the trace pass on this handle.  All forms march the same rays with the same fp32 operations (images, running sum and
+ * frame counters are equal bit for bit); they differ in how rays are dealt to lanes.  The reference has one form, the compute
+ * dispatch of raytrace.comp (pipeline.rs:88-96).  AUTO picks per frame: the wavefront under FULL lighting where it applies,
+ * else the sequential kernel (VXRT_WAVE=0 / VXRT_POOL=1 in the environment change what AUTO picks). */
+#define VXRT_TRACE_AUTO       0
+#define VXRT_TRACE_SEQUENTIAL 1   /* k_trace_fast / k_trace_general: a warp keeps its 32 pixels through their rays            */
+#define VXRT_TRACE_POOL       2   /* k_trace_pool: per-warp ray rings inside one kernel (FULL lighting; measured slower)       */
+#define VXRT_TRACE_WAVEFRONT  3   /* trace_wave.cu: primary stage, then per level a ray-queue march and a resolve pass (FULL) */
+int  vxrt_set_trace_form(VxrtHandle* h, int form);
 
 /* ---- image-space sharding plan: pure host arithmetic, usable without a device ------------------------ */
 /* rows[2r], rows[2r+1] = band [begin,end) of rank r: contiguous, edges on multiples of 8 rows

@@ -6,7 +6,7 @@ lib = sys.argv[1] if len(sys.argv) > 1 else "raytrace_b200/libvxrt.so"
 want = sys.argv[2] if len(sys.argv) > 2 else "ILi2ELb1ELb0E"
 d = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", sys.argv[3] if len(sys.argv) > 3 and not sys.argv[3].startswith("-") else "trace_fast", os.path.abspath(lib)], cwd=d, check=True, stdout=subprocess.DEVNULL)
-cub = [f for f in os.listdir(d) if f.endswith(".cubin")][0]
+cub = max([f for f in os.listdir(d) if f.endswith(".cubin")], key=lambda f: os.path.getsize(os.path.join(d, f)))
 sass = subprocess.run(["nvdisasm", "-c", os.path.join(d, cub)], capture_output=True, text=True).stdout.split("\n")
 res = subprocess.run(["cuobjdump", "-res-usage", os.path.join(d, cub)], capture_output=True, text=True).stdout
 for m in re.finditer(r"Function (\S+):\n\s*(REG:\d+).*?(SHARED:\d+)", res):

@@ -20,6 +20,7 @@ MODE_PRIMARY, MODE_SHADOW, MODE_FULL = 0, 1, 2
 # vxrt_create flags
 FLAG_HIT_BUFFERS, FLAG_DENOISE, FLAG_FINALIZE, FLAG_ACCUMULATE, FLAG_PONG_SWAP, FLAG_GENERAL_MARCH, FLAG_REPROJECT = 1, 2, 4, 8, 16, 64, 128
 FLAG_RAY_HANDOFF = 256
+TRACE_AUTO, TRACE_SEQUENTIAL, TRACE_POOL, TRACE_WAVEFRONT = 0, 1, 2, 3   # vxrt_set_trace_form
 # VxrtBufferId
 (BUF_OUTPUT, BUF_LIGHTING, BUF_DEPTH, BUF_NORMAL, BUF_ALBEDO, BUF_EMISSION, BUF_FOG, BUF_HIT_VOXEL, BUF_HIT_FACE,
  BUF_HIT_WORD, BUF_HIT_T, BUF_STEPS, BUF_RAYS, BUF_ACCUM, BUF_LIGHTING_RAW, BUF_HIT_POS, BUF_HISTORY, BUF_COMPLETED) = range(18)
@@ -96,6 +97,7 @@ SYMBOLS = {
     "vxrt_cuda_stream": (C.c_void_p, [_H]),
     "vxrt_frame_stats": (C.c_int, [_H, C.POINTER(VxrtFrameStats)]),
     "vxrt_launches_per_frame": (C.c_int, [_H]),
+    "vxrt_set_trace_form": (C.c_int, [_H, C.c_int]),
     "vxrt_plan_bands": (C.c_int, [C.c_int, C.c_int, C.c_void_p]),
     "vxrt_plan_bands_weighted": (C.c_int, [C.c_int, C.c_int, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "vxrt_row_costs": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_size_t]),

@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libvxrt.so")
 HOST_OUT = os.path.join(HERE, "vxrt_main")
-SOURCES = ["api.cu", "trace.cu", "trace_fast.cu", "trace_pool.cu", "post.cu", "temporal.cu", "world.cu", "comm.cu", "peer.cu", "chunk_store.cpp"]
+SOURCES = ["api.cu", "trace.cu", "trace_fast.cu", "trace_pool.cu", "trace_wave.cu", "post.cu", "temporal.cu", "world.cu", "comm.cu", "peer.cu", "chunk_store.cpp"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-ffp-contract=off,-fno-fast-math", "-shared"]
 

@@ -214,6 +214,8 @@ int world_write_end(VxrtHandle* h, const int* box = nullptr /* x0 y0 z0 ex ey ez
         p.kind = cudaMemcpyDeviceToDevice;
         CU(cudaMemcpy3DAsync(&p, h->stream));
     }
+    if (h->d_field_nib) CU(vxrt_launch_field_to_nibbles(h->d_minefield, h->d_field_nib, h->cfg.nx, h->cfg.ny, h->cfg.nz, box, h->stream));
+    if (h->d_field_brick) CU(vxrt_launch_field_to_bricks(h->d_minefield, h->d_field_brick, h->cfg.nx, h->cfg.ny, h->cfg.nz, box, h->stream));
     if (h->sharers.empty()) return VXRT_OK;
     CU(cudaEventRecord(h->ev_world, h->stream));
     h->world_version++;
@@ -395,7 +397,7 @@ static int create_impl(const VxrtConfig* cfg, VxrtHandle* owner, VxrtHandle** ou
 
     auto init = [&]() -> int {
         // load every kernel now: a lazy load at first launch cannot complete while a peer-mode kernel spins on a flag
-        CU(vxrt_preload_trace()); CU(vxrt_preload_trace_fast()); CU(vxrt_preload_trace_pool()); CU(vxrt_preload_post()); CU(vxrt_preload_world()); CU(vxrt_preload_peer()); CU(vxrt_preload_temporal());
+        CU(vxrt_preload_trace()); CU(vxrt_preload_trace_fast()); CU(vxrt_preload_trace_pool()); CU(vxrt_preload_trace_wave()); CU(vxrt_preload_post()); CU(vxrt_preload_world()); CU(vxrt_preload_peer()); CU(vxrt_preload_temporal());
         CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
         for (int i = 0; i < 5; i++) CU(cudaEventCreate(&h->ev[i]));
         CU(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
@@ -418,8 +420,12 @@ static int create_impl(const VxrtConfig* cfg, VxrtHandle* owner, VxrtHandle** ou
             // a wash (0.1354 vs 0.1378 ms) and costs a second copy, so those read the linear array.  VXRT_FIELD=lin|tex|texn overrides.
             const char* fm = getenv("VXRT_FIELD");
             h->field_mode = !fm ? ((cfg->nx == 2048 && cfg->ny == 2048 && cfg->nz == 256) ? 1 : 0)      // (the window the texture forms are built for)
-                                : !strcmp(fm, "tex") ? 1 : !strcmp(fm, "texn") ? 2 : 0;
-            if (h->field_mode) {
+                                : !strcmp(fm, "tex") ? 1 : !strcmp(fm, "texn") ? 2 : !strcmp(fm, "brick") ? 3 : !strcmp(fm, "nib") ? 4 : 0;
+            if (h->field_mode == 3) {
+                if ((rc = alloc_zero(h, (void**)&h->d_field_brick, V))) return rc;
+            } else if (h->field_mode == 4) {
+                if ((rc = alloc_zero(h, (void**)&h->d_field_nib, V / 2))) return rc;
+            } else if (h->field_mode) {
                 cudaChannelFormatDesc cd = cudaCreateChannelDesc<unsigned char>();
                 CU(cudaMalloc3DArray(&h->field_arr, &cd, make_cudaExtent((size_t)cfg->nx, (size_t)cfg->ny, (size_t)cfg->nz)));
                 cudaResourceDesc rd; memset(&rd, 0, sizeof rd);
@@ -461,7 +467,11 @@ static int create_impl(const VxrtConfig* cfg, VxrtHandle* owner, VxrtHandle** ou
         if (cfg->mode == VXRT_MODE_FULL && !(cfg->flags & (VXRT_FLAG_HIT_BUFFERS | VXRT_FLAG_REPROJECT)) && cfg->width <= 4096 && cfg->height <= 4096)
             { if ((rc = alloc_zero(h, &h->d_pool_ctx, P * 16))) return rc;       // k_trace_pool's pixel records
               int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->device);
-              if ((rc = alloc_zero(h, &h->d_pool_rings, vxrt_trace_pool_ring_bytes(sms)))) return rc; }
+              if ((rc = alloc_zero(h, &h->d_pool_rings, vxrt_trace_pool_ring_bytes(sms)))) return rc;
+              // the wavefront form's entry / ray / result arrays (trace_wave.cu): one entry per pixel of the band at most
+              const size_t band = (size_t)(h->trace_row1 - h->trace_row0) * cfg->width;
+              if ((rc = alloc_zero(h, &h->d_wave, vxrt_trace_wave_bytes(band)))) return rc;
+              vxrt_trace_wave_carve(&h->wave, h->d_wave, band); }
         if (cfg->flags & VXRT_FLAG_ACCUMULATE) {
             if (owner) {                                                 // one running sum for the whole group of handles
                 if (!owner->d_accum || owner->cfg.width != cfg->width || owner->cfg.height != cfg->height || owner->row0 != h->row0 || owner->row1 != h->row1) {
@@ -526,13 +536,15 @@ void vxrt_destroy(VxrtHandle* h) {
     }
     for (int i = 0; i < 2; i++) if (h->field_tex[i] && !h->world_owner) cudaDestroyTextureObject(h->field_tex[i]);
     if (h->field_arr && !h->world_owner) cudaFreeArray(h->field_arr);
+    if (h->d_field_brick && !h->world_owner) cudaFree(h->d_field_brick);
+    if (h->d_field_nib && !h->world_owner) cudaFree(h->d_field_nib);
     for (int i = 0; i < 2; i++) { if (h->graphs[i].exec) cudaGraphExecDestroy(h->graphs[i].exec); if (h->graphs[i].graph) cudaGraphDestroy(h->graphs[i].graph); }
     if (h->ev_accum) cudaEventDestroy(h->ev_accum);
     if (h->ev_world) cudaEventDestroy(h->ev_world);
     void* ptrs[] = {h->d_materials, h->d_minefield, h->d_noise, h->d_lut, h->d_dirty, h->d_edits, h->d_edit_table, h->d_lighting, h->d_pong,
                     h->d_lighting_raw, h->d_depth, h->d_normal, h->d_albedo, h->d_emission, h->d_fog, h->d_out_buf[0], h->d_out_buf[1],
                     h->d_hit_voxel, h->d_hit_face, h->d_hit_word, h->d_hit_t, h->d_steps, h->d_rays, h->d_accum, h->d_counters, h->d_pool_ctx, h->d_pool_rings,
-                    h->d_hit_pos[0], h->d_hit_pos[1], h->d_hist[0], h->d_hist[1], h->d_completed};
+                    h->d_hit_pos[0], h->d_hit_pos[1], h->d_hist[0], h->d_hist[1], h->d_completed, h->d_wave};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 2; i++) { if (h->h_edits[i]) cudaFreeHost(h->h_edits[i]); if (h->ev_edits[i]) cudaEventDestroy(h->ev_edits[i]); }
     for (int i = 0; i < 5; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
@@ -921,11 +933,13 @@ int vxrt_render_frame(VxrtHandle* h) {
     P.steps = h->d_steps; P.rays = h->d_rays;
     P.accum = h->d_accum;
     P.pool_ctx = (h->cfg.flags & VXRT_FLAG_RAY_HANDOFF) ? nullptr : h->d_pool_ctx; P.pool_rings = h->d_pool_rings;
+    P.wave = h->wave; P.trace_form = h->trace_form;
     if (h->d_hist[0]) h->hist_idx ^= 1;                                  // this frame's records; [hist_idx ^ 1] = the frame before
     P.hit_pos = h->d_hit_pos[h->hist_idx];
     P.counters = h->d_counters;
     P.one2 = 0x3F8000003F800000ull;
-    P.field = wo->field_mode; P.field_tex = wo->field_mode ? (unsigned long long)wo->field_tex[wo->field_mode - 1] : 0ull;
+    P.field = wo->field_mode;
+    P.field_tex = wo->field_mode == 3 ? (unsigned long long)wo->d_field_brick : wo->field_mode == 4 ? (unsigned long long)wo->d_field_nib : wo->field_mode ? (unsigned long long)wo->field_tex[wo->field_mode - 1] : 0ull;
     P.inx = 1.0f / (float)P.nx; P.iny = 1.0f / (float)P.ny; P.inz = 1.0f / (float)P.nz;
 
     // the image goes to the buffer an asynchronous read-back is not using (vxrt_read_output_async)
@@ -943,7 +957,8 @@ int vxrt_render_frame(VxrtHandle* h) {
     // against the host or other streams stays outside: the world / running-sum waits above, the read-back wait below.
     static const bool no_graph = getenv("VXRT_NO_GRAPH") != nullptr;
     const bool shared_sum = h->d_accum && (h->accum_borrowed || !h->sharers.empty());
-    if (!no_graph && !h->graph_failed && !h->peer_on && !h->d_hist[0] && !shared_sum) {
+    h->wave_frame = vxrt_trace_wave_applies(P);      // five launches with the frame's parameters: issued launch by launch
+    if (!no_graph && !h->graph_failed && !h->peer_on && !h->d_hist[0] && !shared_sum && !h->wave_frame) {
         if (h->copy_pending[h->out_idx]) {
             CU(cudaStreamWaitEvent(h->stream, h->ev_copy_done[h->out_idx], 0));
             h->copy_pending[h->out_idx] = false;
@@ -1018,11 +1033,18 @@ static int peer_check(VxrtHandle* h) {
     return VXRT_OK;
 }
 
+int vxrt_set_trace_form(VxrtHandle* h, int form) {
+    if (!h) return VXRT_ERR_INVALID;
+    if (form < VXRT_TRACE_AUTO || form > VXRT_TRACE_WAVEFRONT) return fail(h, VXRT_ERR_INVALID, "vxrt_set_trace_form: unknown form");
+    h->trace_form = form;
+    return VXRT_OK;
+}
+
 int vxrt_launches_per_frame(const VxrtHandle* h) {
     if (!h) return VXRT_ERR_INVALID;
     const bool dn = (h->cfg.flags & VXRT_FLAG_DENOISE) != 0, fin = (h->cfg.flags & VXRT_FLAG_FINALIZE) != 0;
     const bool fold = dn && fin && !h->peer_on && getenv("VXRT_FOLD") != nullptr;
-    return 1 + (dn ? 6 : 0) + (fin && !fold ? 1 : 0) + (h->d_hist[0] ? 1 : 0);
+    return (h->wave_frame ? 5 : 1) + (dn ? 6 : 0) + (fin && !fold ? 1 : 0) + (h->d_hist[0] ? 1 : 0);
 }
 
 int vxrt_sync(VxrtHandle* h) {

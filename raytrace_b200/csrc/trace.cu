@@ -221,6 +221,7 @@ const void* vxrt_trace_kernel(const TraceParams& p, dim3* grid, dim3* block, siz
 
 cudaError_t vxrt_launch_trace(const TraceParams& p, cudaStream_t s) {
     if (p.row1 - p.row0 <= 0) return cudaSuccess;
+    if (vxrt_trace_wave_applies(p)) return vxrt_launch_trace_wave(p, s);                // FULL lighting as a wavefront (trace_wave.cu)
     dim3 grid, block;
     size_t smem = 0;
     const void* k = vxrt_trace_kernel(p, &grid, &block, &smem);

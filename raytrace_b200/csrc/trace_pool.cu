@@ -463,7 +463,7 @@ const void* vxrt_trace_pool_kernel(const TraceParams& p, dim3* grid, dim3* block
     // every ~12 finished rays.  Rings in shared memory (7 % L1 hits, 24 warps) or in global memory (24-32 % hits, 30 warps),
     // 40 / 51 / 64 registers, service thresholds 12-24 and 4-8 steps between lane counts all land within 5 % of each other.
     static const bool on_env = getenv("VXRT_POOL") != nullptr;
-    if (!on_env || !p.pool_ctx || !p.pool_rings || p.mode != VXRT_MODE_FULL || p.hit_voxel || p.hit_pos || p.field) return nullptr;
+    if (!(p.trace_form == VXRT_TRACE_POOL || (p.trace_form == VXRT_TRACE_AUTO && on_env)) || !p.pool_ctx || !p.pool_rings || p.mode != VXRT_MODE_FULL || p.hit_voxel || p.hit_pos || p.field) return nullptr;
     if (p.own_row0 > p.row0 || p.own_row1 < p.row1 || p.width > 4096 || p.height > 4096 || p.max_steps > 200000) return nullptr;
     const unsigned long long bytes = (unsigned long long)p.nx * p.ny * p.nz;
     const unsigned long long base = (unsigned long long)p.minefield;

@@ -15,6 +15,23 @@
 #define VXRT_LUT_ALBEDO 1280            // [128] n / 127          (:156-158)
 #define VXRT_LUT_SCREEN 1408            // [width] px / width * 2 - 1, then [height] py / height * 2 - 1   (:296-297)
 
+// trace_wave.cu: buffers of the FULL-lighting tree run as a wavefront (level 0 = the rays that leave the primary hit, level 1 =
+// the rays that leave the first-bounce hit).  An ENTRY is a pixel that reached the level; its two rays (sun, bounce) are rays
+// 2e and 2e + 1 of the level.
+struct WaveBufs {
+    uint32_t* counts;                    // [level] entries pushed, [2 + level] rays queued for the march kernel, [4 + level] next ray it hands out
+    float4* ent_o[2];                    // xyz = offset hit position the two rays start from, w = px | py << 16
+    uint32_t* ent_m[2];                  // face code of the hit | noise.x << 8 | noise.y << 16 | (level 1: sun1 saw the sky) << 24
+    uint32_t* ent_w;                     // level 1: voxel word of the first-bounce hit
+    // march queue of a level, one slot per ray that outlived its first steps (trace_wave_dev.cuh wave_start_ray):
+    float4* rq_p[2];                     // position, w = ray number (2e: shadow ray of entry e, 2e + 1: its bounce ray)
+    float4* rq_d[2];                     // direction as trace_ray marches it (normalised again, :83), w = occupancy texel at the position
+    float4* rq_l[2];                     // 1 / |direction| per axis (:88), w = iterations of :113's limit to go
+    float4* res_p[2];                    // per ENTRY, bounce ray that hit: offset stop position (:166-180), w = texel offset of the stop voxel
+    uint32_t* res_f[2];                  // per RAY: ended in the sky (bit 0) | face code << 1 | (E4) start in a solid / NaN << 4
+    uint32_t cap;                        // entries per level the buffers hold (pixels of the band)
+};
+
 // Per-frame constants handed to the kernels by value (fits the 4 KB parameter space).
 struct TraceParams {
     // frame block (structs.rs:3-31), decoded
@@ -48,10 +65,14 @@ struct TraceParams {
     unsigned long long* counters;        // [0]=rays [1]=steps [2]=hits [3]=noise fetches [4]=limit exhausted
     unsigned long long one2;             // {1.0f, 1.0f}: a multiplicand ptxas cannot see through (trace_fast.cu (E14))
     // occupancy field as a 3-D texture over a block-linear cudaArray (layout A/B): 0 = linear array + LDG,
-    // 1 = integer texel coordinates, 2 = normalised coordinates with wrap addressing (the unit does the floor and the mod)
+    // 1 = integer texel coordinates, 2 = normalised coordinates with wrap addressing (the unit does the floor and the mod),
+    // 3 = plain memory in 8x8x8 bricks (field_tex then holds the device address of the bricked copy), 4 = plain memory at 4 bits
+    // per voxel, x-neighbours paired (field_tex = the address of that copy)
     int field; unsigned long long field_tex; float inx, iny, inz;
     void* pool_ctx;                      // 16 bytes per pixel for k_trace_pool (trace_pool.cu), or NULL
     void* pool_rings;                    // its per-warp rings (vxrt_trace_pool_ring_bytes)
+    WaveBufs wave;                       // counts == NULL: no wavefront buffers on this handle
+    int trace_form;                      // VXRT_TRACE_* (vxrt_set_trace_form)
 };
 
 // temporal.cu: old_origin / old_transform_c0..2 of the frame block (pipeline.rs:213-227) and the images of the pass
@@ -92,6 +113,8 @@ struct VxrtHandle {
     // layout A/B (VXRT_FIELD=tex|texn at create): a copy of the occupancy field in a block-linear cudaArray, refreshed after every
     // world write, read through texture objects [0] = integer coordinates, [1] = normalised + wrap
     int field_mode = 0; cudaArray_t field_arr = nullptr; cudaTextureObject_t field_tex[2] = {0, 0};
+    uint8_t* d_field_nib = nullptr;      // VXRT_FIELD=nib: the same at 4 bits per voxel (half the bytes)
+    uint8_t* d_field_brick = nullptr;    // VXRT_FIELD=brick: the same copy in plain memory as 8x8x8-voxel bricks of 512 contiguous bytes
     std::vector<uint8_t> h_noise;        // host copy: the seed texel is read on the host (raytrace.comp:298-303)
     uint32_t* d_dirty;                   // one flag per 64^3 chunk
     void* d_edits; size_t edits_cap;
@@ -105,6 +128,9 @@ struct VxrtHandle {
     int32_t* d_hit_voxel; uint8_t* d_hit_face; uint32_t* d_hit_word; float* d_hit_t; uint32_t* d_steps; uint8_t* d_rays;
     float4* d_accum;
     void* d_pool_ctx = nullptr;          // k_trace_pool's per-pixel records (FULL lighting without hit buffers)
+    int trace_form = 0;                  // VXRT_TRACE_* preference of this handle
+    bool wave_frame = false;             // the last frame's trace pass ran as a wavefront
+    void* d_wave = nullptr; WaveBufs wave = {};   // trace_wave.cu: entry / ray / result arrays of the wavefront form (FULL lighting)
     void* d_pool_rings = nullptr;        // and its per-warp rings
     // temporal reprojection (temporal.cu): hit records and {mean light, count} of this frame and the one before
     float4* d_hit_pos[2] = {nullptr, nullptr}; float4* d_hist[2] = {nullptr, nullptr}; ushort4* d_completed = nullptr; int hist_idx = 0;
@@ -154,6 +180,13 @@ const void* vxrt_trace_pool_kernel(const TraceParams& p, dim3* grid, dim3* block
 cudaError_t vxrt_preload_trace_pool();
 size_t vxrt_trace_pool_ring_bytes(int sms);
 const void* vxrt_trace_fast_kernel(const TraceParams& p, dim3* grid, dim3* block);
+const void* vxrt_trace_fast_wave_kernel(const TraceParams& p, dim3* grid, dim3* block);   // the primary stage of the wavefront form, or NULL
+// trace_wave.cu: the FULL-lighting trace pass as a wavefront (primary stage, march, resolve, march, resolve)
+bool vxrt_trace_wave_applies(const TraceParams& p);
+cudaError_t vxrt_launch_trace_wave(const TraceParams& p, cudaStream_t s);
+cudaError_t vxrt_preload_trace_wave();
+size_t vxrt_trace_wave_bytes(size_t entries);
+void vxrt_trace_wave_carve(WaveBufs* w, void* base, size_t entries);
 // finalize.comp folded into the last denoise pass (post.cu k_denoise<.., FIN>): the images finalize reads besides lighting/depth
 struct VxrtFinalizeFold { const uchar4* albedo; const uchar4* emission; const uchar4* fog; const uint8_t* noise; uchar4* out; int row0, row1; };
 cudaError_t vxrt_launch_denoise(const ushort4* src, ushort4* dst, const uint16_t* depth, const uint8_t* normal,
@@ -171,4 +204,6 @@ cudaError_t vxrt_launch_apply_edits(uint32_t* materials, uint32_t* dirty, const 
                                     int nx, int ny, int nz, void* table /* 12 bytes per slot */, size_t table_slots /* pow2 >= 4n */, cudaStream_t s);
 cudaError_t vxrt_launch_compare_chunk(const uint8_t* minefield, const uint8_t* d_stored, int nx, int ny, int cx, int cy, int cz,
                                       unsigned long long* d_out /* [0] mismatching bytes, [1] first offset */, cudaStream_t s);
+cudaError_t vxrt_launch_field_to_nibbles(const uint8_t* minefield, uint8_t* nibbles, int nx, int ny, int nz, const int* box, cudaStream_t s);
+cudaError_t vxrt_launch_field_to_bricks(const uint8_t* minefield, uint8_t* bricks, int nx, int ny, int nz, const int* box, cudaStream_t s);
 cudaError_t vxrt_launch_generate(uint32_t* materials, int nx, int ny, int nz, int kind, uint32_t seed, cudaStream_t s);

@@ -236,11 +236,46 @@ __global__ void __launch_bounds__(256) k_generate(uint32_t* __restrict__ materia
     }
 }
 
+
+// Layout A/B (VXRT_FIELD=brick): the occupancy field once more, as 8x8x8-voxel bricks of 512 contiguous bytes
+// (bricks x fastest; inside a brick x fastest).  One thread moves one 8-byte x-row of a brick; a warp reads 32 consecutive rows
+// of one (y, z) line - coalesced - and stores them 512 bytes apart.  Only the bricks that meet the written box are rewritten.
+__global__ void __launch_bounds__(256) k_field_to_bricks(const uint8_t* __restrict__ lin, uint8_t* __restrict__ bricks, int nx, int ny,
+                                                        int bx0, int y0, int z0, int nbx, int ey, int ez) {
+    const size_t n = (size_t)nbx * ey * ez;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const int bx = bx0 + (int)(i % nbx); const size_t r = i / nbx;
+        const int y = y0 + (int)(r % ey), z = z0 + (int)(r / ey);
+        const uint2 v = *reinterpret_cast<const uint2*>(lin + ((size_t)z * ny + y) * nx + (size_t)bx * 8);
+        const size_t brick = ((size_t)(z >> 3) * (ny >> 3) + (y >> 3)) * (nx >> 3) + bx;
+        *reinterpret_cast<uint2*>(bricks + brick * 512 + (z & 7) * 64 + (y & 7) * 8) = v;
+    }
+}
+
+
+// Layout A/B (VXRT_FIELD=nib): the occupancy field at 4 bits per voxel (its values are 0..6), two x-neighbours per
+// byte, even x in the low nibble: half the footprint - the 128 MiB field of the 512^3 window becomes 64 MiB and fits L2.  One
+// thread packs 16 voxels (one 16-byte load, one 8-byte store); only the rows that meet the written box are rewritten.
+__global__ void __launch_bounds__(256) k_field_to_nibbles(const uint8_t* __restrict__ lin, uint8_t* __restrict__ nib, int nx, int ny,
+                                                         int gx0, int y0, int z0, int ngx, int ey, int ez) {
+    const size_t n = (size_t)ngx * ey * ez;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const int gx = gx0 + (int)(i % ngx); const size_t r = i / ngx;
+        const int y = y0 + (int)(r % ey), z = z0 + (int)(r / ey);
+        const size_t row = ((size_t)z * ny + y) * nx;
+        const uint4 v = *reinterpret_cast<const uint4*>(lin + row + (size_t)gx * 16);
+        auto pack = [](uint32_t w) { return (w & 0xFu) | ((w >> 4) & 0xF0u) | ((w >> 8) & 0xF00u) | ((w >> 12) & 0xF000u); };   // 4 bytes -> 16 bits
+        uint2 o;
+        o.x = pack(v.x) | (pack(v.y) << 16); o.y = pack(v.z) | (pack(v.w) << 16);
+        *reinterpret_cast<uint2*>(nib + (row >> 1) + (size_t)gx * 8) = o;
+    }
+}
+
 }  // namespace
 
 // see peer.cu: every kernel is loaded when a handle is created (a lazy load cannot complete under a spinning kernel)
 #define VXRT_PRELOAD(k) do { cudaFuncAttributes a_; cudaError_t e_ = cudaFuncGetAttributes(&a_, k); if (e_ != cudaSuccess) return e_; } while (0)
-cudaError_t vxrt_preload_world() { VXRT_PRELOAD(k_build_minefield); VXRT_PRELOAD(k_claim_edits); VXRT_PRELOAD(k_apply_edits); VXRT_PRELOAD(k_generate); VXRT_PRELOAD(k_compare_chunk); return cudaSuccess; }
+cudaError_t vxrt_preload_world() { VXRT_PRELOAD(k_build_minefield); VXRT_PRELOAD(k_claim_edits); VXRT_PRELOAD(k_apply_edits); VXRT_PRELOAD(k_generate); VXRT_PRELOAD(k_compare_chunk); VXRT_PRELOAD(k_field_to_bricks); VXRT_PRELOAD(k_field_to_nibbles); return cudaSuccess; }
 
 cudaError_t vxrt_launch_compare_chunk(const uint8_t* minefield, const uint8_t* d_stored, int nx, int ny, int cx, int cy, int cz,
                                       unsigned long long* d_out, cudaStream_t s) {
@@ -266,6 +301,28 @@ cudaError_t vxrt_launch_apply_edits(uint32_t* materials, uint32_t* dirty, const 
     const unsigned blocks = (unsigned)((n + 255) / 256);
     k_claim_edits<<<blocks, 256, 0, s>>>(d_edits, n, nx, ny, nz, keys, winner, (uint32_t)(table_slots - 1));
     k_apply_edits<<<blocks, 256, 0, s>>>(materials, dirty, d_edits, n, nx, ny, nz, keys, winner, (uint32_t)(table_slots - 1));
+    return cudaGetLastError();
+}
+
+cudaError_t vxrt_launch_field_to_bricks(const uint8_t* minefield, uint8_t* bricks, int nx, int ny, int nz, const int* box, cudaStream_t s) {
+    const int whole[6] = {0, 0, 0, nx, ny, nz};
+    const int* b = box ? box : whole;
+    const int bx0 = b[0] >> 3, bx1 = (b[0] + b[3] + 7) >> 3;              // whole 8-byte rows; y and z per row, so no rounding there
+    const size_t n = (size_t)(bx1 - bx0) * b[4] * b[5];
+    if (n == 0) return cudaSuccess;
+    const size_t blocks = (n + 255) / 256;
+    k_field_to_bricks<<<(unsigned)(blocks > 148 * 32 ? 148 * 32 : blocks), 256, 0, s>>>(minefield, bricks, nx, ny, bx0, b[1], b[2], bx1 - bx0, b[4], b[5]);
+    return cudaGetLastError();
+}
+
+cudaError_t vxrt_launch_field_to_nibbles(const uint8_t* minefield, uint8_t* nibbles, int nx, int ny, int nz, const int* box, cudaStream_t s) {
+    const int whole[6] = {0, 0, 0, nx, ny, nz};
+    const int* b = box ? box : whole;
+    const int gx0 = b[0] >> 4, gx1 = (b[0] + b[3] + 15) >> 4;             // whole groups of 16 voxels
+    const size_t n = (size_t)(gx1 - gx0) * b[4] * b[5];
+    if (n == 0) return cudaSuccess;
+    const size_t blocks = (n + 255) / 256;
+    k_field_to_nibbles<<<(unsigned)(blocks > 148 * 32 ? 148 * 32 : blocks), 256, 0, s>>>(minefield, nibbles, nx, ny, gx0, b[1], b[2], gx1 - gx0, b[4], b[5]);
     return cudaGetLastError();
 }
 

@@ -8,9 +8,8 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
-# k_trace_pool (trace_pool.cu) is opt-in and the library reads the switch once per process: the GPU suite runs with it on, so
-# every FULL-lighting handle WITHOUT hit buffers takes the pool and every handle with them the sequential form - both are compared
-os.environ.setdefault("VXRT_POOL", "1")
+# The suite runs the library's defaults (the sequential form of the trace pass); the pool form (trace_pool.cu) and the wavefront form
+# (trace_wave.cu) are selected per handle by the tests that cover them (vxrt_set_trace_form).
 
 
 def pytest_configure(config):

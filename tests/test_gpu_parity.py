@@ -632,7 +632,7 @@ def test_duplicate_edits_last_entry_wins(orc, world):
 @pytest.mark.parametrize("scene,width,height,lr", [("c1", 256, 256, (0, 0, 0)), ("mid", 320, 200, (0, 0, 0)), ("small", 72, 40, (0, 0, 0)),
                                                    ("mid", 200, 120, (16, 0, -16))])
 def test_ray_pool_is_invisible(orc, world, noise, scene, width, height, lr):
-    """trace_pool.cu (VXRT_POOL=1): a FULL-lighting handle without hit buffers runs k_trace_pool (rays decoupled from lanes, refilled from a
+    """trace_pool.cu (vxrt_set_trace_form POOL): a FULL-lighting handle without hit buffers runs k_trace_pool (rays decoupled from lanes, refilled from a
     per-warp queue).  Every ray and every fp32 operation of a pixel is that of the sequential form (k_trace_fast, which a handle
     WITH hit buffers runs), so the images, the running sum and the frame counters are equal bit for bit, and both match the
     oracle."""
@@ -641,13 +641,13 @@ def test_ray_pool_is_invisible(orc, world, noise, scene, width, height, lr):
     dims = scenes.WORLDS[scene][0]
     m, f = world(scene)
     frames = []
-    assert os.environ.get("VXRT_POOL"), "run with VXRT_POOL=1 (tests/conftest.py sets it: the library reads it once per process)"
     for k in range(3):
         cam = scenes.camera(dims, k, 3)
         o = tuple(c + l for c, l in zip(cam["origin"], lr))
         frames.append(orc.fill_frame(o, cam["heading"], cam["pitch"], cam["sun_angle"], 40 + k, lr))
     with R.Renderer(width, height, dims, N.MODE_FULL, N.FLAG_HIT_BUFFERS | N.FLAG_ACCUMULATE) as seq, \
          R.Renderer(width, height, dims, N.MODE_FULL, N.FLAG_ACCUMULATE) as pool:
+        pool.set_trace_form(N.TRACE_POOL)
         for r in (seq, pool):
             r.upload_blue_noise(noise); r.upload_world(m, f)
         fr = orc.Frame(width, height, accumulate=True)
@@ -662,4 +662,41 @@ def test_ray_pool_is_invisible(orc, world, noise, scene, width, height, lr):
                 assert np.array_equal(seq.read_buffer(buf), pool.read_buffer(buf)), buf
             assert np.array_equal(pool.read_buffer(N.BUF_DEPTH), ref.depth) and np.array_equal(pool.read_buffer(N.BUF_NORMAL), ref.normal)
             d = np.abs(pool.read_buffer(N.BUF_LIGHTING).astype(np.int64) - ref.lighting.astype(np.int64)).max()
+            assert d <= C16_TOL, d
+
+
+@pytest.mark.parametrize("scene,width,height,lr", [("c1", 256, 256, (0, 0, 0)), ("mid", 320, 200, (0, 0, 0)), ("small", 72, 40, (0, 0, 0)),
+                                                   ("mid", 200, 120, (16, 0, -16))])
+def test_wavefront_is_invisible(orc, world, noise, scene, width, height, lr):
+    """trace_wave.cu (vxrt_set_trace_form WAVEFRONT): the FULL-lighting tree cut at its rays - primary stage, then per level a
+    ray-queue march with lane refill and a resolve pass.  Every ray and every fp32 operation of a pixel is that of the sequential
+    form (which a handle WITH hit buffers runs), so the images, the running sum and the frame counters are equal bit for bit, and
+    both match the oracle."""
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    dims = scenes.WORLDS[scene][0]
+    m, f = world(scene)
+    frames = []
+    for k in range(3):
+        cam = scenes.camera(dims, k, 3)
+        o = tuple(c + l for c, l in zip(cam["origin"], lr))
+        frames.append(orc.fill_frame(o, cam["heading"], cam["pitch"], cam["sun_angle"], 40 + k, lr))
+    with R.Renderer(width, height, dims, N.MODE_FULL, N.FLAG_HIT_BUFFERS | N.FLAG_ACCUMULATE) as seq, \
+         R.Renderer(width, height, dims, N.MODE_FULL, N.FLAG_ACCUMULATE) as wave:
+        wave.set_trace_form(N.TRACE_WAVEFRONT)
+        for r in (seq, wave):
+            r.upload_blue_noise(noise); r.upload_world(m, f)
+        fr = orc.Frame(width, height, accumulate=True)
+        for blk in frames:
+            ref = orc.render(m, f, noise, blk, N.MODE_FULL, width, height, frame=fr)
+            for r in (seq, wave):
+                r.set_frame(blk); r.render_frame()
+            assert wave.launches_per_frame() == 5, "the wavefront form did not run"
+            a, b = seq.frame_stats(), wave.frame_stats()
+            assert (a.rays, a.steps, a.hits, a.noise_fetches, a.limit_exhausted) == (b.rays, b.steps, b.hits, b.noise_fetches, b.limit_exhausted)
+            assert (b.rays, b.steps, b.hits) == (ref.stats.rays, ref.stats.steps, ref.stats.hits)
+            for buf in (N.BUF_DEPTH, N.BUF_NORMAL, N.BUF_ALBEDO, N.BUF_EMISSION, N.BUF_FOG, N.BUF_LIGHTING, N.BUF_ACCUM):
+                assert np.array_equal(seq.read_buffer(buf), wave.read_buffer(buf)), buf
+            assert np.array_equal(wave.read_buffer(N.BUF_DEPTH), ref.depth) and np.array_equal(wave.read_buffer(N.BUF_NORMAL), ref.normal)
+            d = np.abs(wave.read_buffer(N.BUF_LIGHTING).astype(np.int64) - ref.lighting.astype(np.int64)).max()
             assert d <= C16_TOL, d

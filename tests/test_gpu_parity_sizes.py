@@ -102,6 +102,74 @@ def test_c3_at_size(orc, noise, world512):
         assert s.limit_exhausted == ref.stats.ub_limit_exhausted == 0
 
 
+def _compare_images(ref, r, N):
+    """A handle without the parity buffers: the G-buffer bit for bit, colour within the tolerances of test_gpu_parity.py."""
+    from test_gpu_parity import C16_TOL
+    B = r.read_buffer
+    for buf, want in ((N.BUF_DEPTH, ref.depth), (N.BUF_NORMAL, ref.normal), (N.BUF_ALBEDO, ref.albedo), (N.BUF_EMISSION, ref.emission)):
+        assert np.array_equal(B(buf), want), buf
+    d = lambda a, b: int(np.max(np.abs(a.astype(np.int64) - b.astype(np.int64)), initial=0))
+    assert d(B(N.BUF_FOG), ref.fog) <= C8_TOL and d(B(N.BUF_LIGHTING), ref.lighting) <= C16_TOL
+    assert d(B(N.BUF_OUTPUT), ref.output) <= C8_TOL
+
+
+def test_c3_wavefront_at_size(orc, noise, world512):
+    """BASELINE config 3 without parity buffers and with the trace pass in its wavefront form (trace_wave.cu):
+    running mean over 4 frames at 1080p against the oracle, frame counters included."""
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    dims = scenes.WORLDS["c2"][0]
+    m, f = world512
+    W, H = 1920, 1080
+    fr = orc.Frame(W, H, accumulate=True)
+    with R.Renderer(W, H, dims, N.MODE_FULL, N.FLAG_DENOISE | N.FLAG_FINALIZE | N.FLAG_ACCUMULATE) as r:
+        r.set_trace_form(N.TRACE_WAVEFRONT)
+        r.upload_blue_noise(noise); r.upload_world(m, f)
+        for seed in range(1, 5):
+            blk = _block(orc, dims, 0, 1, seed)
+            ref = orc.render(m, f, noise, blk, N.MODE_FULL, W, H, denoise=True, finalize=True, frame=fr)
+            r.set_frame(blk); r.render_frame()
+        assert r.launches_per_frame() == 5 + 6 + 1, "the wavefront form did not run"
+        _compare_images(ref, r, N)
+        acc = r.read_buffer(N.BUF_ACCUM)
+        assert np.array_equal(acc[..., 3], fr.accum[..., 3])
+        assert np.allclose(acc[..., :3], fr.accum[..., :3], rtol=1e-5, atol=1e-5)
+        s = r.frame_stats()
+        assert (s.rays, s.steps, s.hits, s.noise_fetches) == (ref.stats.rays, ref.stats.steps, ref.stats.hits, ref.stats.noise_fetches)
+        assert s.limit_exhausted == ref.stats.ub_limit_exhausted == 0
+
+
+@pytest.mark.parametrize("field,mode", [("brick", 1), ("brick", 2), ("nib", 1), ("nib", 2), ("tex", 2), ("texn", 2)])
+def test_occupancy_field_layouts(orc, noise, world512, field, mode):
+    """Layout A/B (VXRT_FIELD): the occupancy field read from a copy in 8x8x8-voxel bricks, at 4 bits per voxel, or through the
+    texture unit.  Same texels at other addresses, so every buffer equals the oracle's as with the linear array; an edit list goes
+    through the box-limited refresh of the copy."""
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    dims = scenes.WORLDS["c2"][0]
+    m, f = world512
+    W, H = 640, 360
+    old = os.environ.get("VXRT_FIELD")
+    os.environ["VXRT_FIELD"] = field
+    try:
+        with R.Renderer(W, H, dims, mode, N.FLAG_HIT_BUFFERS | N.FLAG_DENOISE | N.FLAG_FINALIZE) as r:
+            r.upload_blue_noise(noise); r.upload_world(m, f)
+            blk = _block(orc, dims, 9, 64, 3)
+            ref = orc.render(m, f, noise, blk, mode, W, H, denoise=True, finalize=True)
+            r.set_frame(blk); r.render_frame()
+            _compare(ref, r, N, denoise=True, finalize=True)
+            if mode == 2:
+                e = orc.generate_edits(2000, *dims, 11, 0)
+                r.apply_edits(e)
+                m2, f2 = r.read_world()
+                ref = orc.render(m2, f2, noise, blk, mode, W, H, denoise=True, finalize=True)
+                r.set_frame(blk); r.render_frame()
+                _compare(ref, r, N, denoise=True, finalize=True)
+    finally:
+        if old is None: del os.environ["VXRT_FIELD"]
+        else: os.environ["VXRT_FIELD"] = old
+
+
 def test_c5_at_size(orc, noise, world512):
     """BASELINE config 5: one frame's 10 000 edits on the 512^3 world (device: scatter + rebuild of the touched chunks;
     oracle: set_block + pack_into of the same chunks), the whole window compared, then a 1080p full-lighting frame."""
@@ -232,6 +300,16 @@ def test_c4_at_size(orc, noise):
         ref = orc.render(m, f, noise, blk, N.MODE_FULL, W, H, denoise=True, finalize=True)
         r.set_frame(blk); r.render_frame()
         _compare(ref, r, N, denoise=True, finalize=True)
+        s = r.frame_stats()
+        assert (s.rays, s.steps, s.hits, s.noise_fetches) == (ref.stats.rays, ref.stats.steps, ref.stats.hits, ref.stats.noise_fetches)
+        assert s.limit_exhausted == ref.stats.ub_limit_exhausted
+    # the same frame without parity buffers, trace pass in its wavefront form, occupancy field through the texture unit
+    with R.Renderer(W, H, dims, N.MODE_FULL, N.FLAG_DENOISE | N.FLAG_FINALIZE) as r:
+        r.set_trace_form(N.TRACE_WAVEFRONT)
+        r.upload_blue_noise(noise); r.generate_world(kind, seed)
+        r.set_frame(blk); r.render_frame()
+        assert r.launches_per_frame() == 5 + 6 + 1, "the wavefront form did not run"
+        _compare_images(ref, r, N)
         s = r.frame_stats()
         assert (s.rays, s.steps, s.hits, s.noise_fetches) == (ref.stats.rays, ref.stats.steps, ref.stats.hits, ref.stats.noise_fetches)
         assert s.limit_exhausted == ref.stats.ub_limit_exhausted
