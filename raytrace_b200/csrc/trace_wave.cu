@@ -27,7 +27,7 @@ namespace {
 
 constexpr int MW = 4;                          // warps per CTA of the march kernel (each works alone)
 #ifndef VXRT_WAVE_MINB
-#define VXRT_WAVE_MINB 12                      // CTAs per SM: 40 registers
+#define VXRT_WAVE_MINB 16                      // CTAs per SM: 32 registers, every warp slot (the march is latency-bound)
 #endif
 #ifndef VXRT_WAVE_IDLE
 #define VXRT_WAVE_IDLE 12                      // finished lanes that end a march phase while the level still has rays to hand out
