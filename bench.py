@@ -486,6 +486,29 @@ def run_vxrt(args, rank, world_size, local_rank, shard="bands", dist=None):
     if reads:
         for b in out_host:
             r.host_unregister(b)
+    # What the host side of this box can take: every rank that delivers frames copies a device buffer of one image's size to
+    # page-locked host memory with plain cudaMemcpyAsync calls (torch), all ranks at once, untimed work outside the metric.  Beside
+    # the rate the end-to-end loop reached it says whether the library or the host is the limit at N GPUs.
+    d2h_probe = None
+    if reads:
+        nb = W * H * 4
+        src = torch.empty(nb, dtype=torch.uint8, device=f"cuda:{local_rank}")
+        dst = torch.empty(nb, dtype=torch.uint8).pin_memory()
+        n_probe = max(8, min(256, int(2e9 // nb)))
+        for _ in range(2):
+            dst.copy_(src, non_blocking=True)
+        torch.cuda.synchronize()
+        barrier()
+        p0 = time.perf_counter()
+        for _ in range(n_probe):
+            dst.copy_(src, non_blocking=True)
+        torch.cuda.synchronize()
+        p1 = time.perf_counter()
+        my_frames = args.steps
+        d2h_probe = {"plain_copy_gbs_rank0": nb * n_probe / (p1 - p0) / 1e9, "e2e_loop_gbs_rank0": nb * my_frames / e2e_s / 1e9,
+                     "copies": n_probe, "bytes": nb,
+                     "note": "plain pinned cudaMemcpyAsync of one image per call, every delivering rank at once, against the D2H rate of the end-to-end loop"}
+    barrier()
 
     # ---- band mode: the root's image against a single-GPU frame of the same block (untimed) -----------------
     bands_match = None
@@ -572,7 +595,7 @@ def run_vxrt(args, rank, world_size, local_rank, shard="bands", dist=None):
             "kernel_ms_per_step_by_rank": per_rank,
             "trace_mrays_per_s_rank0": tot["rays"] / trace_s / 1e6,
             "e2e": {"value": rays / e2e_s / 1e6, "unit": "Mrays/s", "frames_per_s": args.steps * nf / e2e_s,
-                    "h2d_bytes_per_step": (192 + 16 * ne) * nf, "d2h_bytes_per_step": W * H * 4 * nf},
+                    "h2d_bytes_per_step": (192 + 16 * ne) * nf, "d2h_bytes_per_step": W * H * 4 * nf, "d2h_probe": d2h_probe},
             # per frame and rank: the handle's kernels (vxrt_launches_per_frame); peer mode adds k_halo_push + 3 k_peer_sync (+1 on the root)
             "gpu_launches": args.steps * (launches_per_frame * world_size + ((4 * world_size + 1) if world_size > 1 and args.comm == "peer" and not by_frames else 0)),
             "roofline": {"kernel": "k_trace_fast", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",

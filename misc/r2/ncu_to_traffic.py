@@ -2,8 +2,8 @@
 """misc/r2/ncu_to_traffic.py — profiles/ncu_traffic.json (what bench.py's roofline.traffic / roofline.ncu quote) from the committed
 full-set summaries of the trace pass, one entry per workload."""
 import csv, json
-SRC = [("c2", "profiles/r2_p_c2_frame_ncu_full_summary.csv"), ("c3", "profiles/r2_p_c3_trace_ncu_full_summary.csv"),
-       ("c4", "profiles/r2_p_c4_trace_ncu_full_summary.csv")]
+SRC = [("c2", "profiles/r2_w_c2_frame_ncu_full_summary.csv"), ("c3", "profiles/r2_w_c3_trace_ncu_full_summary.csv"),
+       ("c4", "profiles/r2_w_c4_trace_ncu_full_summary.csv")]
 SCALE = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1e-3, "us": 1, "ms": 1e3, "msecond": 1e3, "usecond": 1, "nsecond": 1e-3, "s": 1e6}
 out = {}
 for w, p in SRC:
@@ -18,6 +18,6 @@ for w, p in SRC:
               "lanes_per_instruction": v("smsp__thread_inst_executed_per_inst_executed.ratio"),
               "warp_instructions": v("smsp__inst_executed.sum"), "l2_hit_pct": v("lts__t_sector_hit_rate.pct"),
               "launch_us_under_ncu": v("gpu__time_duration.sum"),
-              "source": p + " (ncu --set full --clock-control none, one launch, L2 flushed before the frame; misc/r2/run_p.sh)"}
+              "source": p + " (ncu --set full --clock-control none, one launch, L2 flushed before the frame; misc/r2/run_w.sh)"}
 json.dump(out, open("profiles/ncu_traffic.json", "w"), indent=1)
 print({w: (round(o["dram_bytes_per_launch"] / 1e6, 1), o["launch_us_under_ncu"]) for w, o in out.items()})
