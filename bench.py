@@ -490,22 +490,22 @@ def run_vxrt(args, rank, world_size, local_rank, shard="bands", dist=None):
     # page-locked host memory with plain cudaMemcpyAsync calls (torch), all ranks at once, untimed work outside the metric.  Beside
     # the rate the end-to-end loop reached it says whether the library or the host is the limit at N GPUs.
     d2h_probe = None
+    nb = W * H * 4
+    n_probe = max(8, min(256, int(2e9 // nb)))
     if reads:
-        nb = W * H * 4
         src = torch.empty(nb, dtype=torch.uint8, device=f"cuda:{local_rank}")
         dst = torch.empty(nb, dtype=torch.uint8).pin_memory()
-        n_probe = max(8, min(256, int(2e9 // nb)))
         for _ in range(2):
             dst.copy_(src, non_blocking=True)
         torch.cuda.synchronize()
-        barrier()
+    barrier()                                    # every rank, reading or not
+    if reads:
         p0 = time.perf_counter()
         for _ in range(n_probe):
             dst.copy_(src, non_blocking=True)
         torch.cuda.synchronize()
         p1 = time.perf_counter()
-        my_frames = args.steps
-        d2h_probe = {"plain_copy_gbs_rank0": nb * n_probe / (p1 - p0) / 1e9, "e2e_loop_gbs_rank0": nb * my_frames / e2e_s / 1e9,
+        d2h_probe = {"plain_copy_gbs_rank0": nb * n_probe / (p1 - p0) / 1e9, "e2e_loop_gbs_rank0": nb * args.steps / e2e_s / 1e9,
                      "copies": n_probe, "bytes": nb,
                      "note": "plain pinned cudaMemcpyAsync of one image per call, every delivering rank at once, against the D2H rate of the end-to-end loop"}
     barrier()
