@@ -4,7 +4,7 @@ N=${1:-2}; tag=${2:-r2_mg$N}
 mkdir -p gpurun_out
 nvidia-smi -L > gpurun_out/${tag}_gpus.txt
 ( timeout 900 python -m pytest tests/test_multi_gpu.py -m gpu -v ) > gpurun_out/${tag}_pytest_multi_gpu.txt 2>&1; echo "pytest rc=$?"; tail -6 gpurun_out/${tag}_pytest_multi_gpu.txt
-for w in c2 c3 c4; do
+for w in c2 c3 c4 c5; do
   timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $N --workload $w --steps 32 --sustained-seconds 0 > gpurun_out/${tag}_bench_$w.json 2> gpurun_out/${tag}_bench_$w.err; echo "bench $w rc=$?"
   python - <<PY
 import json
