@@ -412,7 +412,21 @@ static int create_impl(const VxrtConfig* cfg, VxrtHandle* owner, VxrtHandle** ou
             h->d_materials = owner->d_materials; h->d_minefield = owner->d_minefield; h->d_noise = owner->d_noise;
         } else {
             if ((rc = alloc_zero(h, (void**)&h->d_materials, V * 4))) return rc;
-            if ((rc = alloc_zero(h, (void**)&h->d_minefield, V))) return rc;
+            // the occupancy field inside ONE 4 GiB line of the address space, so that the march's 32-bit address form (E15) - and with
+            // it the kernels with baked window dims, the texture forms and the wavefront - applies whatever address cudaMalloc hands
+            // out (a 1 GiB field crossed a line in two of five processes on the B200: those ran the 64-bit form, 2.8 instead of 2.26 ms
+            // per C4 trace pass).  A block that crosses is replaced by one of twice the size, which holds a window that does not.
+            if ((rc = alloc_zero(h, (void**)&h->d_minefield_base, V))) return rc;
+            h->d_minefield = h->d_minefield_base;
+            {
+                const unsigned long long b = (unsigned long long)h->d_minefield_base, line = (b + V - 1) & ~0xFFFFFFFFull;   // the 4 GiB line inside [b, b + V), if any
+                if ((line > b || getenv("VXRT_FIELD_REALLOC") /* test hook: take this path whatever the address */) && V <= 0x80000000ull) {
+                    cudaFree(h->d_minefield_base); h->d_minefield_base = nullptr;
+                    if ((rc = alloc_zero(h, (void**)&h->d_minefield_base, 2 * V))) return rc;
+                    const unsigned long long b2 = (unsigned long long)h->d_minefield_base, l2 = (b2 + V - 1) & ~0xFFFFFFFFull;
+                    h->d_minefield = reinterpret_cast<uint8_t*>(l2 > b2 ? l2 : b2);      // the line itself is 4 GiB-aligned, and l2 + V <= b2 + 2V
+                }
+            }
             if ((rc = alloc_zero(h, (void**)&h->d_noise, h->h_noise.size()))) return rc;
             if ((rc = alloc_zero(h, (void**)&h->d_dirty, (size_t)(cfg->nx >> 6) * (cfg->ny >> 6) * (cfg->nz >> 6) * 4))) return rc;
             // Occupancy field through the texture unit where it does not fit L2: measured on the 1 GiB field of C4
@@ -541,7 +555,7 @@ void vxrt_destroy(VxrtHandle* h) {
     for (int i = 0; i < 2; i++) { if (h->graphs[i].exec) cudaGraphExecDestroy(h->graphs[i].exec); if (h->graphs[i].graph) cudaGraphDestroy(h->graphs[i].graph); }
     if (h->ev_accum) cudaEventDestroy(h->ev_accum);
     if (h->ev_world) cudaEventDestroy(h->ev_world);
-    void* ptrs[] = {h->d_materials, h->d_minefield, h->d_noise, h->d_lut, h->d_dirty, h->d_edits, h->d_edit_table, h->d_lighting, h->d_pong,
+    void* ptrs[] = {h->d_materials, h->d_minefield_base, h->d_noise, h->d_lut, h->d_dirty, h->d_edits, h->d_edit_table, h->d_lighting, h->d_pong,
                     h->d_lighting_raw, h->d_depth, h->d_normal, h->d_albedo, h->d_emission, h->d_fog, h->d_out_buf[0], h->d_out_buf[1],
                     h->d_hit_voxel, h->d_hit_face, h->d_hit_word, h->d_hit_t, h->d_steps, h->d_rays, h->d_accum, h->d_counters, h->d_pool_ctx, h->d_pool_rings,
                     h->d_hit_pos[0], h->d_hit_pos[1], h->d_hist[0], h->d_hist[1], h->d_completed, h->d_wave};

@@ -110,6 +110,7 @@ struct VxrtHandle {
     // on the owner) and the passes after it overlap the next frame's trace pass
     bool accum_borrowed = false; cudaEvent_t ev_accum = nullptr; VxrtHandle* accum_last = nullptr;
     uint32_t* d_materials; uint8_t* d_minefield; uint8_t* d_noise; float* d_lut;
+    uint8_t* d_minefield_base = nullptr; // the allocation d_minefield lies in (api.cu: the field never crosses a 4 GiB line)
     // layout A/B (VXRT_FIELD=tex|texn at create): a copy of the occupancy field in a block-linear cudaArray, refreshed after every
     // world write, read through texture objects [0] = integer coordinates, [1] = normalised + wrap
     int field_mode = 0; cudaArray_t field_arr = nullptr; cudaTextureObject_t field_tex[2] = {0, 0};

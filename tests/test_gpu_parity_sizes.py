@@ -262,6 +262,15 @@ def test_noncubic_window_64bit_addressing():
     assert p.returncode == 0 and "no-a32 ok" in p.stdout, p.stdout[-2000:] + p.stderr[-4000:]
 
 
+def test_field_allocation_inside_one_4gib_line(orc, noise, monkeypatch):
+    """The occupancy field is placed so that it never crosses a 4 GiB line of the address space (the 32-bit address form, the kernels
+    with baked dims, the texture forms and the wavefront all need that); a block that would cross is replaced by one of twice the
+    size.  VXRT_FIELD_REALLOC=1 takes that path whatever address cudaMalloc returned; the frame must not notice."""
+    monkeypatch.setenv("VXRT_FIELD_REALLOC", "1")
+    _noncubic_case(orc, noise)
+    monkeypatch.delenv("VXRT_FIELD_REALLOC")
+
+
 def test_start_relocation_with_tiny_dir_y(orc, world, noise):
     """raytrace.comp:312-315 with the camera outside the -y face and a pixel column whose |dir.y| is ~1e-5: the relocated
     start is millions of voxels away, beyond what the lean march's floor trick covers.  vxrt_render_frame
