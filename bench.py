@@ -55,7 +55,8 @@ WORKLOADS = {
 }
 EDITS_PER_FRAME = {"c5": 10000}
 EDIT_SEED = 7
-IN_FLIGHT = {"c1": 2, "c2": 2, "c3": 1, "c4": 1}   # frames in flight per GPU (--in-flight 0); c3 can chain two handles through the
+IN_FLIGHT = {"c1": 4, "c2": 2, "c3": 1, "c4": 1}   # frames in flight per GPU (--in-flight 0; measured 1..4, misc/r2/run_z.sh: C2 2939 / 3529 / 3516 / 3516 frames/s,
+                                                    # C1 12.6k / 23.9k / 31.2k / 38.7k, C4 315 / 286 / 286 / 287); c3 can chain two handles through the
                                                     # shared running sum (--in-flight 2) but measures no gain: 0.672 against 0.660 ms
 MODE_NAMES = {0: "primary", 1: "primary+shadow", 2: "full"}
 
