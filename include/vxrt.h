@@ -236,8 +236,9 @@ int  vxrt_frame_stats(VxrtHandle* h, VxrtFrameStats* out);  /* syncs the stream 
 int  vxrt_launches_per_frame(const VxrtHandle* h);
 /* Form of the trace pass on this handle.  All forms march the same rays with the same fp32 operations (images, running sum and
  * frame counters are equal bit for bit); they differ in how rays are dealt to lanes.  The reference has one form, the compute
- * dispatch of raytrace.comp (pipeline.rs:88-96).  AUTO picks per frame: the wavefront under FULL lighting where it applies,
- * else the sequential kernel (VXRT_WAVE=0 / VXRT_POOL=1 in the environment change what AUTO picks). */
+ * dispatch of raytrace.comp (pipeline.rs:88-96).  AUTO is the sequential kernel; under FULL lighting it hands the second bounce
+ * ray of a pixel to a finished lane of its warp once the caller's vxrt_frame_stats calls have shown more than 28 march steps per
+ * ray (VXRT_NO_AUTO_HANDOFF=1 turns that off; VXRT_WAVE=1 / VXRT_POOL=1 in the environment make AUTO pick those forms). */
 #define VXRT_TRACE_AUTO       0
 #define VXRT_TRACE_SEQUENTIAL 1   /* k_trace_fast / k_trace_general: a warp keeps its 32 pixels through their rays            */
 #define VXRT_TRACE_POOL       2   /* k_trace_pool: per-warp ray rings inside one kernel (FULL lighting; measured slower)       */

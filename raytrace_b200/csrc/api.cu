@@ -948,6 +948,13 @@ int vxrt_render_frame(VxrtHandle* h) {
     P.accum = h->d_accum;
     P.pool_ctx = (h->cfg.flags & VXRT_FLAG_RAY_HANDOFF) ? nullptr : h->d_pool_ctx; P.pool_rings = h->d_pool_rings;
     P.wave = h->wave; P.trace_form = h->trace_form;
+    {   // AUTO: where the caller's own vxrt_frame_stats calls have shown long rays (an edited world: C5 marches 40 steps per ray, C3 14,
+        // C4 18), the second bounce ray of a pixel is handed to a finished lane of its warp ((E16), trace_fast.cu) - same rays, same
+        // images and counters; measured 0.966 -> 0.899 ms per C5 trace pass, and a loss below ~25 steps per ray
+        static const bool no_auto = getenv("VXRT_NO_AUTO_HANDOFF") != nullptr;
+        if (!no_auto && h->trace_form == VXRT_TRACE_AUTO && P.mode == VXRT_MODE_FULL && h->steps_per_ray > 28.0f && wo->field_mode != 1)
+            P.flags |= VXRT_FLAG_RAY_HANDOFF;
+    }
     if (h->d_hist[0]) h->hist_idx ^= 1;                                  // this frame's records; [hist_idx ^ 1] = the frame before
     P.hit_pos = h->d_hit_pos[h->hist_idx];
     P.counters = h->d_counters;
@@ -1172,6 +1179,7 @@ int vxrt_frame_stats(VxrtHandle* h, VxrtFrameStats* out) {
     { const int rc = peer_check(h); if (rc) return rc; }
     if (c[6]) return fail(h, VXRT_ERR_STATE, "k_trace_pool: a ray ring overflowed (trace_pool.cu); the frame is void");
     out->rays = c[0]; out->steps = c[1]; out->hits = c[2]; out->noise_fetches = c[3]; out->limit_exhausted = c[4];
+    if (c[0]) h->steps_per_ray = (float)((double)c[1] / (double)c[0]);                  // what AUTO picks the trace form by (vxrt_render_frame)
     CU(cudaEventElapsedTime(&out->trace_ms, h->ev[0], h->ev[1]));
     CU(cudaEventElapsedTime(&out->denoise_ms, h->ev[1], h->ev[2]));
     CU(cudaEventElapsedTime(&out->finalize_ms, h->ev[2], h->ev[3]));

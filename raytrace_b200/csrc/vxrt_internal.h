@@ -130,6 +130,7 @@ struct VxrtHandle {
     float4* d_accum;
     void* d_pool_ctx = nullptr;          // k_trace_pool's per-pixel records (FULL lighting without hit buffers)
     int trace_form = 0;                  // VXRT_TRACE_* preference of this handle
+    float steps_per_ray = 0.0f;          // of the last frame whose counters the caller read (vxrt_frame_stats); 0 = unknown
     bool wave_frame = false;             // the last frame's trace pass ran as a wavefront
     void* d_wave = nullptr; WaveBufs wave = {};   // trace_wave.cu: entry / ray / result arrays of the wavefront form (FULL lighting)
     void* d_pool_rings = nullptr;        // and its per-warp rings

@@ -747,3 +747,31 @@ def test_trace_forms_agree_on_random_cameras(orc, world, noise, scene, width, he
         finally:
             for r in others:
                 r.close()
+
+
+def test_auto_handoff_on_long_rays_is_invisible(orc, world, noise):
+    """AUTO form policy (vxrt_render_frame): once vxrt_frame_stats has shown more than 28 march steps per ray - a heavily edited
+    world - a FULL-lighting handle hands second bounce rays to finished lanes.  Frames before and after the switch equal those of a
+    handle with parity buffers (always the plain sequential form) bit for bit."""
+    import raytrace_b200 as R
+    from raytrace_b200 import _native as N, scenes
+    dims = scenes.WORLDS["mid"][0]
+    m, f = world("mid")
+    width, height = 256, 144
+    e = orc.generate_edits(60000, *dims, 5, 0)           # solid specks all over the window: short steps, long rays
+    with R.Renderer(width, height, dims, N.MODE_FULL, N.FLAG_HIT_BUFFERS | N.FLAG_ACCUMULATE) as seq, \
+         R.Renderer(width, height, dims, N.MODE_FULL, N.FLAG_ACCUMULATE) as auto:
+        for r in (seq, auto):
+            r.upload_blue_noise(noise); r.upload_world(m, f); r.apply_edits(e)
+        ratios = []
+        for k in range(4):
+            cam = scenes.camera(dims, k, 4)
+            blk = orc.fill_frame(cam["origin"], cam["heading"], cam["pitch"], cam["sun_angle"], 70 + k)
+            for r in (seq, auto):
+                r.set_frame(blk); r.render_frame()
+            a, b = seq.frame_stats(), auto.frame_stats()
+            assert (a.rays, a.steps, a.hits, a.noise_fetches, a.limit_exhausted) == (b.rays, b.steps, b.hits, b.noise_fetches, b.limit_exhausted), k
+            ratios.append(b.steps / max(b.rays, 1))
+            for buf in (N.BUF_DEPTH, N.BUF_NORMAL, N.BUF_ALBEDO, N.BUF_FOG, N.BUF_LIGHTING, N.BUF_ACCUM):
+                assert np.array_equal(seq.read_buffer(buf), auto.read_buffer(buf), equal_nan=True), (k, buf)
+        assert ratios[0] > 28.0 and max(ratios[:-1]) > 28.0, ("the scene is meant to cross the policy's threshold after its first frame", ratios)
