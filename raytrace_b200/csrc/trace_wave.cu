@@ -15,7 +15,7 @@
 //   k_wave_march (level 1)
 //   k_wave_resolve<1>        light2, albedo, the pixel's light (:338-348)
 //
-// The march kernel holds nothing but rays (no shading code, 40 registers, 48 warps per SM), and everything with a chain of
+// The march kernel holds nothing but rays (no shading code, 32 registers, 64 warps per SM), and everything with a chain of
 // dependent fetches (noise -> tables -> first texel, the voxel word of a hit) runs one thread per entry on full warps.  Every ray
 // is the ray of the sequential form - same origin, direction, steps, the same fp32 operations - and a pixel's light is summed
 // in the order of :320-350, so images, running sum and frame counters equal k_trace_fast's bit for bit
