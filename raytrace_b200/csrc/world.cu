@@ -6,6 +6,7 @@
 //                      generator draws from thread_rng and is not reproducible)
 #include "vxrt_internal.h"
 #include <mutex>
+#include <cooperative_groups.h>
 
 namespace {
 
@@ -104,6 +105,115 @@ __global__ void __launch_bounds__(512) k_build_minefield(uint32_t* __restrict__ 
                              nibble_to_bytes((uint32_t)(L2[(z >> 2) * 16 + (y >> 2)] >> sh) & 15u) + nibble_to_bytes((uint32_t)(L3[(z >> 3) * 8 + (y >> 3)] >> sh) & 15u) +
                              nibble_to_bytes((uint32_t)(L4[(z >> 4) * 4 + (y >> 4)] >> sh) & 15u) + nibble_to_bytes((uint32_t)(L5[(z >> 5) * 2 + (y >> 5)] >> sh) & 15u);
         __stcs(reinterpret_cast<uint32_t*>(minefield + base + ((size_t)z * ny + y) * nx + x4 * 4), 0x06060606u - cnt);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_build_minefield_half: the same result from half the instructions and twice the CTAs.  ncu on the kernel above (C5, 512 chunks,
+// profiles/r2_z): 104 M warp instructions at 53 % issue, 0.86 waves of 512-thread CTAs with every CTA in the same phase (read,
+// levels, write), DRAM at 34 % of peak.  Three changes:
+//   * a chunk is two 32-slab halves in z, one 256-thread CTA each: the levels up to L5 (32^3 cubes) never look across the halves,
+//     so 1024 CTAs of mixed phases keep the memory system busy.  The one chunk-wide fact - pack_into wipes the words of a wholly
+//     empty chunk (chunk.rs:155-161) - is exchanged between the two CTAs of a thread-block cluster through distributed shared
+//     memory; the occupancy value is 6 whether its 32-cube or its whole chunk is empty, so it needs no exchange;
+//   * the levels are nested (S in L1 in ... in L5), so the value - the index of the first level whose bit is set, 6 if none - has
+//     the bit planes  b0 = L1&~S | L3&~L2 | L5&~L4,  b1 = L3&~L1 | ~L5,  b2 = ~L3  as 64-bit row masks: a dozen logic operations per
+//     ROW instead of six nibble spreads and five adds per four voxels;
+//   * a thread stores 16 voxels (one 16-byte store) from one 16-bit field of each plane.
+// ---------------------------------------------------------------------------------------------
+#ifndef VXRT_BUILD_MINB
+#define VXRT_BUILD_MINB 8                          // 32 registers, 2048 threads per SM: the 1024 CTAs of a 512-chunk window are one wave (measured 6 / 7 / 8: 136 / 113 / 110 us)
+#endif
+__device__ __forceinline__ uint32_t planes_to_bytes(uint32_t f0, uint32_t f1, uint32_t f2, int g) {   // voxels 4g .. 4g+3 of a 16-bit field triple
+    return nibble_to_bytes((f0 >> (4 * g)) & 15u) | (nibble_to_bytes((f1 >> (4 * g)) & 15u) << 1) | (nibble_to_bytes((f2 >> (4 * g)) & 15u) << 2);
+}
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(256, VXRT_BUILD_MINB) k_build_minefield_half(uint32_t* __restrict__ materials, uint8_t* __restrict__ minefield,
+                                                                                       int nx, int ny, int nz, const uint32_t* __restrict__ dirty) {
+    const int chunk = blockIdx.x >> 1, half = blockIdx.x & 1;                  // the cluster's two CTAs: z slabs [0,32) and [32,64) of one chunk
+    if (dirty && !dirty[chunk]) return;                                        // (both CTAs of the cluster leave)
+    __shared__ unsigned long long S[32 * 64];                                  // solid bits of voxel row (z, y), z in the half
+    __shared__ unsigned long long L1[16 * 32], L2[8 * 16], L3[4 * 8], L4[2 * 4], L5[1 * 2];
+    __shared__ uint32_t s_flags[2];                                            // this half: [0] any solid voxel, [1] any nonzero word
+    cooperative_groups::cluster_group cluster = cooperative_groups::this_cluster();
+    const int cxn = nx >> 6, cyn = ny >> 6;
+    const int cx = chunk % cxn, cy = (chunk / cxn) % cyn, cz = chunk / (cxn * cyn);
+    const size_t base = ((size_t)(cz * 64 + half * 32) * ny + cy * 64) * nx + cx * 64;
+    const int tid = threadIdx.x;
+    uint32_t* S32 = reinterpret_cast<uint32_t*>(S);
+    for (int i = tid; i < 32 * 64 * 2; i += 256) S32[i] = 0;
+    if (tid < 2) s_flags[tid] = 0;
+    __syncthreads();
+    // pass 1: four voxels per load; q = z*1024 + y*16 + x4
+    uint32_t any_word = 0, any_solid = 0;
+#pragma unroll 8
+    for (int it = 0; it < 128; it++) {
+        const int q = tid + it * 256, x4 = q & 15, y = (q >> 4) & 63, z = q >> 10;
+        const uint4 w = __ldcs(reinterpret_cast<const uint4*>(materials + base + ((size_t)z * ny + y) * nx + x4 * 4));
+        const uint32_t nib = ((w.x >> 15) & 1u) | ((w.y >> 14) & 2u) | ((w.z >> 13) & 4u) | ((w.w >> 12) & 8u);
+        any_word |= w.x | w.y | w.z | w.w;
+        any_solid |= nib;
+        if (nib) atomicOr(&S32[(z * 64 + y) * 2 + (x4 >> 3)], nib << ((x4 & 7) * 4));
+    }
+    if (__any_sync(0xffffffffu, any_solid != 0) && (tid & 31) == 0) s_flags[0] = 1;
+    if (__any_sync(0xffffffffu, any_word != 0) && (tid & 31) == 0) s_flags[1] = 1;
+    cluster.sync();                                                            // (also this CTA's barrier after pass 1)
+    const uint32_t* peer = cluster.map_shared_rank(s_flags, cluster.block_rank() ^ 1u);
+    const bool half_empty = s_flags[0] == 0, chunk_empty = half_empty && peer[0] == 0;          // chunk.rs:155-161
+    const bool wipe = chunk_empty && s_flags[1] != 0;
+    cluster.sync();                                                            // the peer's flags are not read after this point: either CTA may exit
+    if (half_empty) {
+        // no solid in this half: every voxel 6 (its 32-cubes are empty; so is the chunk, or the value is 6 anyway); words wiped
+        // only for a wholly empty chunk that still holds nonzero words
+        for (int it = 0; it < 32; it++) {
+            const int q = tid + it * 256, x16 = q & 3, y = (q >> 2) & 63, z = q >> 8;
+            const size_t gi = base + ((size_t)z * ny + y) * nx + x16 * 16;
+            __stcs(reinterpret_cast<uint4*>(minefield + gi), make_uint4(0x06060606u, 0x06060606u, 0x06060606u, 0x06060606u));
+            if (wipe) for (int k = 0; k < 4; k++) *reinterpret_cast<uint4*>(materials + gi + 4 * k) = make_uint4(0, 0, 0, 0);
+        }
+        return;
+    }
+    // levels: OR of the 2x2 rows below, then the in-word spread of that level's group size
+    for (int c = tid; c < 16 * 32; c += 256) {
+        const int y = c & 31, z = c >> 5;
+        const unsigned long long m = S[(2 * z) * 64 + 2 * y] | S[(2 * z) * 64 + 2 * y + 1] | S[(2 * z + 1) * 64 + 2 * y] | S[(2 * z + 1) * 64 + 2 * y + 1];
+        L1[c] = spread_or(m, 1, 0xAAAAAAAAAAAAAAAAull);
+    }
+    __syncthreads();
+    if (tid < 8 * 16) {
+        const int y = tid & 15, z = tid >> 4;
+        const unsigned long long m = L1[(2 * z) * 32 + 2 * y] | L1[(2 * z) * 32 + 2 * y + 1] | L1[(2 * z + 1) * 32 + 2 * y] | L1[(2 * z + 1) * 32 + 2 * y + 1];
+        L2[tid] = spread_or(m, 2, 0xCCCCCCCCCCCCCCCCull);
+    }
+    __syncthreads();
+    if (tid < 4 * 8) {
+        const int y = tid & 7, z = tid >> 3;
+        const unsigned long long m = L2[(2 * z) * 16 + 2 * y] | L2[(2 * z) * 16 + 2 * y + 1] | L2[(2 * z + 1) * 16 + 2 * y] | L2[(2 * z + 1) * 16 + 2 * y + 1];
+        L3[tid] = spread_or(m, 4, 0xF0F0F0F0F0F0F0F0ull);
+    }
+    __syncthreads();
+    if (tid < 2 * 4) {
+        const int y = tid & 3, z = tid >> 2;
+        const unsigned long long m = L3[(2 * z) * 8 + 2 * y] | L3[(2 * z) * 8 + 2 * y + 1] | L3[(2 * z + 1) * 8 + 2 * y] | L3[(2 * z + 1) * 8 + 2 * y + 1];
+        L4[tid] = spread_or(m, 8, 0xFF00FF00FF00FF00ull);
+    }
+    __syncthreads();
+    if (tid < 2) {
+        const int y = tid;                                                      // z = 0: the half is one 32-cube deep
+        const unsigned long long m = L4[2 * y] | L4[2 * y + 1] | L4[4 + 2 * y] | L4[4 + 2 * y + 1];
+        L5[tid] = spread_or(m, 16, 0xFFFF0000FFFF0000ull);
+    }
+    __syncthreads();
+    // pass 2: 16 voxels per thread; value = index of the first set level, as three bit planes of the row
+#pragma unroll 2
+    for (int it = 0; it < 32; it++) {
+        const int q = tid + it * 256, x16 = q & 3, y = (q >> 2) & 63, z = q >> 8;
+        const unsigned long long s0 = S[z * 64 + y], l1 = L1[(z >> 1) * 32 + (y >> 1)], l2 = L2[(z >> 2) * 16 + (y >> 2)], l3 = L3[(z >> 3) * 8 + (y >> 3)],
+                                 l4 = L4[(z >> 4) * 4 + (y >> 4)], l5 = L5[y >> 5];
+        const unsigned long long b0 = (l1 & ~s0) | (l3 & ~l2) | (l5 & ~l4), b1 = (l3 & ~l1) | ~l5, b2 = ~l3;
+        const int sh = x16 * 16;
+        const uint32_t f0 = (uint32_t)(b0 >> sh) & 0xFFFFu, f1 = (uint32_t)(b1 >> sh) & 0xFFFFu, f2 = (uint32_t)(b2 >> sh) & 0xFFFFu;
+        const uint4 v = make_uint4(planes_to_bytes(f0, f1, f2, 0), planes_to_bytes(f0, f1, f2, 1), planes_to_bytes(f0, f1, f2, 2), planes_to_bytes(f0, f1, f2, 3));
+        __stcs(reinterpret_cast<uint4*>(minefield + base + ((size_t)z * ny + y) * nx + x16 * 16), v);
     }
 }
 
@@ -275,7 +385,7 @@ __global__ void __launch_bounds__(256) k_field_to_nibbles(const uint8_t* __restr
 
 // see peer.cu: every kernel is loaded when a handle is created (a lazy load cannot complete under a spinning kernel)
 #define VXRT_PRELOAD(k) do { cudaFuncAttributes a_; cudaError_t e_ = cudaFuncGetAttributes(&a_, k); if (e_ != cudaSuccess) return e_; } while (0)
-cudaError_t vxrt_preload_world() { VXRT_PRELOAD(k_build_minefield); VXRT_PRELOAD(k_claim_edits); VXRT_PRELOAD(k_apply_edits); VXRT_PRELOAD(k_generate); VXRT_PRELOAD(k_compare_chunk); VXRT_PRELOAD(k_field_to_bricks); VXRT_PRELOAD(k_field_to_nibbles); return cudaSuccess; }
+cudaError_t vxrt_preload_world() { VXRT_PRELOAD(k_build_minefield); VXRT_PRELOAD(k_build_minefield_half); VXRT_PRELOAD(k_claim_edits); VXRT_PRELOAD(k_apply_edits); VXRT_PRELOAD(k_generate); VXRT_PRELOAD(k_compare_chunk); VXRT_PRELOAD(k_field_to_bricks); VXRT_PRELOAD(k_field_to_nibbles); return cudaSuccess; }
 
 cudaError_t vxrt_launch_compare_chunk(const uint8_t* minefield, const uint8_t* d_stored, int nx, int ny, int cx, int cy, int cz,
                                       unsigned long long* d_out, cudaStream_t s) {
@@ -286,7 +396,11 @@ cudaError_t vxrt_launch_compare_chunk(const uint8_t* minefield, const uint8_t* d
 cudaError_t vxrt_launch_build_minefield(uint32_t* materials, uint8_t* minefield, int nx, int ny, int nz,
                                         const uint32_t* dirty, cudaStream_t s) {
     const int chunks = (nx >> 6) * (ny >> 6) * (nz >> 6);
-    k_build_minefield<<<chunks, 512, 0, s>>>(materials, minefield, nx, ny, nz, dirty);
+    // two 256-thread CTAs (one thread-block cluster) per chunk; VXRT_BUILD_WHOLE=1 runs the one-CTA-per-chunk kernel (A/B, and what
+    // vxrt_apply_edits_static keeps using)
+    static const bool whole = getenv("VXRT_BUILD_WHOLE") != nullptr;
+    if (whole) k_build_minefield<<<chunks, 512, 0, s>>>(materials, minefield, nx, ny, nz, dirty);
+    else k_build_minefield_half<<<2 * chunks, 256, 0, s>>>(materials, minefield, nx, ny, nz, dirty);
     return cudaGetLastError();
 }
 
